@@ -1,0 +1,131 @@
+/* bmpc.h — thin C ABI of the B200-native batched linear-MPC engine (libbmpc.so).
+ *
+ * This is the drop-in boundary for ONE hot path of lms-org/trajectory_controller:
+ *   getTrajectoryPoint()  (src/trajectory_point_follower.cpp:392-443)   -> bmpc_extract_points
+ *   mpcControllerTobi()   (src/trajectory_point_follower.cpp:301-389)   -> bmpc_set_model / bmpc_set_target / bmpc_solve
+ *   dlib::mpc<S,I,N>      (dlib_files/dlib/control/mpc.h:13-365)        -> one engine slot per controller object
+ * The reference crosses no FFI on this path (everything is in-process C++); these entry points are what a C++
+ * facade with dlib::mpc's method set (trajectory_controller_b200/cpp/bmpc_mpc.h) and the module glue bind.
+ *
+ * Conventions
+ *   - every function returns BMPC_OK (0) or a negative bmpc_status; bmpc_last_error() gives the message of the
+ *     last failure on the calling thread.  Nothing throws across this boundary.
+ *   - the caller owns all host pointers; a handle owns its device memory, stream and events.
+ *   - a handle is NOT thread-safe; distinct handles are independent.  One handle = one CUDA device.
+ *   - host arrays are instance-major ("AoS"): element e of instance b at [b*len + e]; matrices are row-major
+ *     like dlib::matrix (matrix_data_layout.h:131-155).  All host numbers are double (dlib's type) whatever the
+ *     compute precision of the handle.
+ *   - calls are synchronous on return unless the name ends in _async; bmpc_sync() waits for those.
+ *   - there is no CPU fallback: without a CUDA device bmpc_create fails with BMPC_E_CUDA.
+ */
+#ifndef BMPC_H
+#define BMPC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bmpc_handle bmpc_t;
+
+typedef enum bmpc_status {
+    BMPC_OK = 0,
+    BMPC_E_INVALID = -1,      /* bad argument (null pointer, count > capacity, time >= horizon, ...) */
+    BMPC_E_UNSUPPORTED = -2,  /* (S,I,N) / precision / mode combination not instantiated in this build */
+    BMPC_E_CUDA = -3,         /* CUDA runtime error, or no usable device */
+    BMPC_E_NOMEM = -4,        /* host or device allocation failed */
+    BMPC_E_STATE = -5         /* call order violated (e.g. solve before set_model) */
+} bmpc_status;
+
+#define BMPC_FP64 64
+#define BMPC_FP32 32
+
+/* EXACT: the reference's floating-point evaluation order, no FMA contraction: results equal dlib::mpc's
+ *        (IEEE value equality; the sign of a zero is the only freedom).  Iteration counts identical.
+ * FAST : same recursion with FMA contraction; tolerance parity only. */
+#define BMPC_MODE_EXACT 0
+#define BMPC_MODE_FAST 1
+
+/* bmpc_solve_* flags */
+#define BMPC_WARM 1u            /* persistent-controller semantics of mpc.h:229-237: shift the stored controls before the
+                                   solve, shift the targets after it, keep controls/v for the next call.  Without it
+                                   every instance behaves like a freshly constructed dlib::mpc
+                                   (src/trajectory_point_follower.cpp:366: controls = 0), and nothing is persisted. */
+#define BMPC_KEEP_CONTROLS 2u   /* cold solves only: also write the full control sequence so bmpc_get_controls works */
+
+/* per-instance status byte written by a solve */
+#define BMPC_ST_MAXITER 1u      /* the loop ended at max_iterations (mpc.h:271) instead of the eps test (mpc.h:310) */
+
+/* ---- lifetime ------------------------------------------------------------------------------------------- */
+/* 1 if the (S,I,N) template shape is instantiated (dlib::mpc is a compile-time template too, mpc.h:13-18). */
+int bmpc_shape_supported(int S, int I, int N);
+/* mpc.h:51-125 for `capacity` controllers at once.  device < 0 = current device. */
+int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precision, int mode, int device);
+void bmpc_destroy(bmpc_t* h);
+const char* bmpc_last_error(void);
+/* Build identity: "bmpc <version> sm_100a ..." */
+const char* bmpc_version(void);
+
+/* ---- model / options  (mpc.h:51-125, :172-214) ------------------------------------------------------------- */
+/* A[S*S] B[S*I] C[S] Q[S] R[I] lower[I] upper[I]; per_instance = 0: one model for every instance;
+ * 1: `count` models, instance-major.  Runs the lambda / Q_diag recursion (mpc.h:114-123) on the device. */
+int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C, const double* Q, const double* R,
+                   const double* lower, const double* upper, int per_instance, int64_t count);
+/* mpc.h:190-214; defaults eps = 0.01, max_iterations = 10000 (mpc.h:103-104).  max_iterations saturates at 2^32-1. */
+int bmpc_set_options(bmpc_t* h, double eps, uint64_t max_iterations);
+int bmpc_get_options(bmpc_t* h, double* eps, uint64_t* max_iterations);
+/* Test observability (dlib keeps these private, mpc.h:360-361): lambda and Q_diag[N*I] of one instance's model. */
+int bmpc_get_derived(bmpc_t* h, int64_t instance, double* lambda, double* q_diag);
+
+/* ---- targets  (mpc.h:142-170) ------------------------------------------------------------------------------ */
+/* time = -1: set_target(val) (all horizon steps); 0..N-1: set_target(val, time); time = N-1 is set_last_target.
+ * per_instance = 0: val[S] for every instance; 1: val[count][S]. */
+int bmpc_set_target(bmpc_t* h, const double* val, int time, int per_instance, int64_t count);
+int bmpc_get_target(bmpc_t* h, int64_t instance, int time, double* val /* [S] */);
+
+/* ---- controller state ------------------------------------------------------------------------------------------ */
+/* Back to freshly constructed controllers: controls = 0, targets = 0 (mpc.h:105-112), v = 0. */
+int bmpc_reset(bmpc_t* h);
+/* controls[count][N][I] of instances first..first+count-1 (what dlib keeps in `controls`, mpc.h:362). */
+int bmpc_get_controls(bmpc_t* h, int64_t first, int64_t count, double* controls);
+/* EXTENSION (dlib::mpc has no such setter): seed the warm start. */
+int bmpc_set_controls(bmpc_t* h, int64_t first, int64_t count, const double* controls);
+
+/* ---- solve  (mpc.h:216-240 operator(), :253-347 solve_linear_mpc) --------------------------------------------- */
+/* Host buffers: x0[count][S] in; u0[count][I], iters[count] (may be NULL), status[count] (may be NULL) out.
+ * Includes the host<->device copies. */
+int bmpc_solve(bmpc_t* h, int64_t count, const double* x0, double* u0, uint32_t* iters, uint8_t* status,
+               unsigned flags);
+/* Device-resident pieces of the same call, for callers that keep the batch in HBM: */
+int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0);            /* H2D + layout change */
+int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags);   /* kernel only, on the handle's stream */
+int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t* status);
+int bmpc_sync(bmpc_t* h);
+/* CUDA-event time of the last solve kernel (ms), the number of kernels this handle has launched so far, and
+ * the launch geometry of the solve kernel (for roofline bookkeeping). */
+int bmpc_last_kernel_ms(bmpc_t* h, float* ms);
+int64_t bmpc_launch_count(bmpc_t* h);
+int bmpc_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* regs);
+/* Measured arithmetic peak of the handle's device, the roofline denominator of the solver (it is bound by the FP64 /
+ * FP32 CUDA-core pipe, not by HBM or tensor cores): register-resident chains; fused = 1: FMA (2 flop/instruction),
+ * fused = 0: separate multiplies and adds as EXACT mode must issue them (1 flop/instruction). */
+int bmpc_probe_peak(bmpc_t* h, int precision, int fused, double* tflops, double* ginstr_per_s);
+
+/* ---- trajectory point  (src/trajectory_point_follower.cpp:392-443) ---------------------------------------------- */
+#define BMPC_PT_INTERPOLATED 0  /* :428-437 */
+#define BMPC_PT_LAST 1          /* :439-442 */
+#define BMPC_PT_EMPTY 2         /* :394-407 */
+/* Polylines as five float arrays; element k of instance b at base[b*stride_instance + k*stride_point]
+ * (stride_instance = 0: one trajectory shared by all instances).  npoints: NULL (all P) or [count].
+ * dist[count] in; idx/flag/pos/dir/vel [count] out.  Index selection and outputs are bit-exact w.r.t. the
+ * sequential-float restatement in oracle/extract_oracle.c. */
+int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints, const float* px, const float* py,
+                        const float* dx, const float* dy, const float* vel, int64_t stride_instance,
+                        int64_t stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* out_px,
+                        float* out_py, float* out_dx, float* out_dy, float* out_vel);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BMPC_H */

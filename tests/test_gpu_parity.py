@@ -1,0 +1,233 @@
+"""Parity of the CUDA path, called through the C ABI, against the golden vectors of the real dlib::mpc and
+against the pinned oracle.   [-m gpu]
+
+Bar (EXACT mode, FP64): IEEE value equality of u0 and of the whole control sequence (the sign of a zero is the only
+freedom: the kernel does not multiply by diagm()'s literal zeros) and IDENTICAL iteration counts.
+"""
+import numpy as np
+import pytest
+
+from _oracle import same_values
+from trajectory_controller_b200 import workloads as W
+from trajectory_controller_b200.engine import EXACT, FP64, BatchedMPC
+
+pytestmark = pytest.mark.gpu
+
+
+def _cold(model, N, x0, target=None, eps=0.01, max_iter=10000, per_instance=False):
+    m = model
+    S = (m["B"] if isinstance(m, dict) else m.B).shape[-2]
+    I = (m["B"] if isinstance(m, dict) else m.B).shape[-1]
+    with BatchedMPC(S, I, N, len(x0), FP64, EXACT) as eng:
+        eng.set_model(m, per_instance=per_instance)
+        eng.set_options(eps, max_iter)
+        if target is not None:
+            eng.set_target(target)
+        u0, it, st = eng.solve(x0, keep_controls=True)
+        return u0, eng.get_controls(len(x0)), it, st, eng.derived(0)
+
+
+# ------------------------------------------------------------------------------------------ golden (real dlib)
+@pytest.mark.parametrize("tag,eps", [("kat_tight", 1e-8), ("kat_default", 0.01)])
+def test_kat_closed_loop_matches_dlib(golden, tag, eps):
+    """dlib's own known-answer scenario (dlib/test/mpc.cpp:269-316) through a persistent engine slot; the batch holds
+    3 copies of the controller to check slots do not interact."""
+    kat = W.kat_model()
+    with BatchedMPC(2, 1, 30, 3) as eng:
+        eng.set_model(kat)
+        eng.set_options(eps, 10000)
+        lam, qd = eng.derived()
+        assert lam == golden[tag + "_lambda"][0] and same_values(qd, golden[tag + "_qdiag"])
+        for k in range(30):
+            x = np.tile(golden[tag + "_x"][k], (3, 1))
+            u0, it, st = eng.solve(x, warm=True)
+            for b in range(3):
+                assert same_values(u0[b], golden[tag + "_u0"][k]), (k, b)
+                assert it[b] == golden[tag + "_iters"][k], (k, b)
+    if tag == "kat_default":
+        assert u0[0, 0] == -0.10000002376964306
+
+
+def test_tobi_module_configuration(golden):
+    """The reference module's own controller: mpc<2,2,4>, fresh per cycle (src/trajectory_point_follower.cpp:366-380)."""
+    u0, _, _, _, _ = _cold(W.tobi_model(1.0), 4, np.zeros((1, 2)), target=np.array([[0.05, 0.1]]))
+    assert tuple(u0[0]) == (0.27357241694602841, 0.023830246920932288)
+    models = [W.tobi_model(float(v)) for v in golden["tobi_rand_v"]]
+    pm = {k: np.stack([getattr(m, k) for m in models]) for k in ("A", "B", "C", "Q", "R", "lower", "upper")}
+    u0, ctr, it, _, _ = _cold(pm, 4, np.zeros((len(models), 2)), target=golden["tobi_rand_target"], per_instance=True)
+    assert same_values(u0, golden["tobi_rand_u0"]) and same_values(ctr, golden["tobi_rand_controls"])
+    assert np.array_equal(it, golden["tobi_rand_iters"])
+
+
+@pytest.mark.parametrize("N", [10, 30, 60, 100])
+def test_bike_cold_matches_dlib(golden, N):
+    x0 = golden[f"bike{N}_cold_x0"]
+    u0, ctr, it, st, _ = _cold(W.bicycle4_model(), N, x0)
+    assert same_values(u0, golden[f"bike{N}_cold_u0"])
+    assert same_values(ctr, golden[f"bike{N}_cold_controls"])
+    assert np.array_equal(it, golden[f"bike{N}_cold_iters"])
+    assert np.array_equal(st, (it >= 10000).astype(np.uint8))
+
+
+def test_bike_closed_loop_with_moving_targets(golden):
+    """Config 1: persistent controller, set_target(val, t) pre-fill, set_last_target each tick, 300 ticks."""
+    bike, N = W.bicycle4_model(), 30
+    with BatchedMPC(4, 1, N, 2) as eng:
+        eng.set_model(bike)
+        for t in range(N):
+            eng.set_target([0.1 * np.sin(0.05 * t), 0, 0, 0], t)
+        for k in range(300):
+            eng.set_last_target([0.1 * np.sin(0.05 * (k + N)), 0, 0, 0])
+            u0, it, _ = eng.solve(np.tile(golden["bike30_loop_x"][k], (2, 1)), warm=True)
+            assert same_values(u0[0], golden["bike30_loop_u0"][k]) and same_values(u0[1], golden["bike30_loop_u0"][k]), k
+            assert it[0] == golden["bike30_loop_iters"][k] == it[1], k
+
+
+def test_sweep_slice_per_instance_models(golden):
+    pm, x0 = W.sweep_models(per_combo=2, seed=44)
+    u0, ctr, it, _, _ = _cold(pm, 10, x0, per_instance=True)
+    assert same_values(u0, golden["sweep10_u0"]) and same_values(ctr, golden["sweep10_controls"])
+    assert np.array_equal(it, golden["sweep10_iters"])
+
+
+# ------------------------------------------------------------------------------------------ oracle differential
+@pytest.mark.parametrize("shape", [(2, 2, 4), (2, 1, 30), (4, 1, 10), (4, 2, 10), (3, 2, 7), (4, 1, 30)])
+def test_random_models_vs_oracle(oracle, shape):
+    S, I, N = shape
+    rng = np.random.default_rng(100 + S * 7 + I * 3 + N)
+    B = 300
+    pm = dict(A=np.eye(S) + 0.3 * rng.standard_normal((B, S, S)), B=rng.standard_normal((B, S, I)),
+              C=0.05 * rng.standard_normal((B, S)), Q=rng.uniform(0, 10, (B, S)) * (rng.random((B, S)) > 0.25),
+              R=rng.uniform(0.01, 2, (B, I)), lower=-rng.uniform(0.1, 1, (B, I)), upper=rng.uniform(0.1, 1, (B, I)))
+    x0 = rng.standard_normal((B, S)); tgt = rng.standard_normal((B, S))
+    with BatchedMPC(S, I, N, B) as eng:
+        eng.set_model(pm, per_instance=True)
+        eng.set_target(tgt)
+        for b in (0, 17, B - 1):
+            lam, qd = eng.derived(b)
+            oc = oracle.controller({k: v[b] for k, v in pm.items()}, N)
+            assert lam == oc.lam and same_values(qd, oc.q_diag())
+        for eps, mi in ((0.01, 10000), (1e-6, 300), (0.5, 49), (0.01, 50), (0.01, 51), (0.01, 0)):
+            eng.set_options(eps, mi)
+            u0, it, st = eng.solve(x0, keep_controls=True)
+            ctr = eng.get_controls(B)
+            uo, co, ito, _ = oracle.batch_cold(pm, N, x0, target=tgt, eps=eps, max_iter=mi, per_instance=True, nthreads=4)
+            assert same_values(u0, uo) and same_values(ctr, co), (shape, eps, mi)
+            assert np.array_equal(it, ito), (shape, eps, mi)
+            assert np.array_equal(st, (ito >= mi).astype(np.uint8))
+
+
+@pytest.mark.parametrize("which", ["bike10", "kat"])
+def test_persistent_controllers_vs_oracle(oracle, which):
+    """Warm batch: per-instance states, per-step targets set at random times, shift semantics (mpc.h:229-237) and the
+    stale-v corner (Q_diag == 0 at the 50th coordinate step, reachable with dlib's KAT model)."""
+    rng = np.random.default_rng(5)
+    if which == "bike10":
+        m, N, B, ticks = W.bicycle4_model(1.3, 10, 3, 0.01), 10, 48, 40
+    else:
+        m, N, B, ticks = W.kat_model(), 30, 16, 12
+    S = m.S
+    ocs = [oracle.controller(m, N) for _ in range(B)]
+    x = rng.standard_normal((B, S)) * (0.3 if which == "bike10" else 2.0)
+    with BatchedMPC(S, m.I, N, B) as eng:
+        eng.set_model(m)
+        for k in range(ticks):
+            if k % 3 == 0:
+                t = int(rng.integers(0, N)); val = rng.standard_normal((B, S)) * 0.1
+                eng.set_target(val, t)
+                for b in range(B):
+                    ocs[b].set_target(val[b], t)
+            if k == 20:
+                val = rng.standard_normal(S) * 0.05
+                eng.set_target(val)                       # all steps, all instances
+                for b in range(B):
+                    ocs[b].set_target(val)
+            u0, it, _ = eng.solve(x, warm=True)
+            uo = np.stack([ocs[b].step(x[b]) for b in range(B)])
+            assert same_values(u0, uo), k
+            assert np.array_equal(it, [ocs[b].iters for b in range(B)]), k
+            if k % 7 == 0:
+                assert same_values(eng.get_controls(B), np.stack([ocs[b].controls() for b in range(B)]))
+                for tt in (0, N // 2, N - 1):
+                    assert same_values(eng.get_target(tt, instance=3), ocs[3].targets()[tt])
+            x = x @ m.A.T + u0 @ m.B.T + 0.01 * rng.standard_normal((B, S))
+
+
+# ------------------------------------------------------------------------------------------ full size, properties
+def test_config2_full_batch_properties(oracle):
+    """BASELINE config 2 at full size (65,536 cold instances, N=30, FP64): spot-check 768 instances against the
+    oracle, then size-independent properties: box feasibility, determinism, batch-order independence."""
+    bike, N, B = W.bicycle4_model(), 30, 65536
+    x0 = W.random_offsets_x0(B, 42)
+    with BatchedMPC(4, 1, N, B) as eng:
+        eng.set_model(bike)
+        u0, it, st = eng.solve(x0)
+        pick = np.random.default_rng(0).choice(B, 768, replace=False)
+        uo, _, ito, _ = oracle.batch_cold(bike, N, x0[pick], nthreads=8, want_controls=False)
+        assert same_values(u0[pick], uo) and np.array_equal(it[pick], ito)
+        assert np.all(np.abs(u0) <= W.ALPHA_MAX) and np.all(it <= 10000) and np.all(st == 0)
+        u1, it1, _ = eng.solve(x0)                                      # determinism / no state leaks in cold mode
+        assert np.array_equal(u0.view(np.uint64), u1.view(np.uint64)) and np.array_equal(it, it1)
+        perm = np.random.default_rng(1).permutation(B)                  # which lane solves an instance is irrelevant
+        u2, it2, _ = eng.solve(x0[perm])
+        assert np.array_equal(u0[perm].view(np.uint64), u2.view(np.uint64)) and np.array_equal(it[perm], it2)
+        # mirror symmetry of the problem: x0 -> -x0 gives u0 -> -u0 with the same iteration counts
+        u3, it3, _ = eng.solve(-x0[:4096])
+        assert same_values(u3, -u0[:4096]) and np.array_equal(it3, it[:4096])
+
+
+def test_ragged_batches_and_capacity(oracle):
+    """count < capacity, count = 1, count not a multiple of the warp size."""
+    bike, N = W.bicycle4_model(), 10
+    x0 = W.random_offsets_x0(1000, 7)
+    uo, _, ito, _ = oracle.batch_cold(bike, N, x0)
+    with BatchedMPC(4, 1, N, 1000) as eng:
+        eng.set_model(bike)
+        for cnt in (1, 31, 33, 257, 1000):
+            u0, it, _ = eng.solve(x0[:cnt])
+            assert same_values(u0, uo[:cnt]) and np.array_equal(it, ito[:cnt]), cnt
+
+
+def test_error_paths_on_device():
+    from trajectory_controller_b200.engine import BmpcError
+    with BatchedMPC(4, 1, 10, 8) as eng:
+        with pytest.raises(BmpcError):
+            eng.solve(np.zeros((4, 4)))                 # no model yet
+        eng.set_model(W.bicycle4_model())
+        with pytest.raises(BmpcError):
+            eng.solve(np.zeros((9, 4)))                 # count > capacity
+        with pytest.raises(BmpcError):
+            eng.set_target(np.zeros(4), 10)             # time >= horizon
+        with pytest.raises(BmpcError):
+            eng.set_options(0.0, 10)                    # eps must be > 0
+        assert eng.get_epsilon() == 0.01 and eng.get_max_iterations() == 10000   # mpc.h:103-104 defaults
+
+
+# ------------------------------------------------------------------------------------------ trajectory point
+def test_extract_points_vs_oracle(oracle):
+    rng = np.random.default_rng(3)
+    B, P = 5000, 64
+    px = np.cumsum(rng.uniform(0.01, 0.2, (B, P)), axis=1).astype(np.float32)
+    py = (0.3 * np.sin(px) + 0.01 * rng.standard_normal((B, P))).astype(np.float32)
+    dx, dy, vel = (rng.standard_normal((B, P)).astype(np.float32) for _ in range(3))
+    dist = rng.uniform(-0.1, 8.0, B).astype(np.float32)
+    npts = rng.integers(0, P + 1, B).astype(np.int32)
+    with BatchedMPC(2, 2, 4, 8) as eng:
+        for layout, arrs in (("bp", (px, py, dx, dy, vel)), ("pb", tuple(np.ascontiguousarray(a.T) for a in (px, py, dx, dy, vel)))):
+            for n in (None, npts):
+                gi, gf, go = eng.extract_points(*arrs, dist, npoints=n, layout=layout)
+                oi, of, oo = oracle.extract(*arrs, dist, npoints=n, layout=layout)
+                assert np.array_equal(gi, oi) and np.array_equal(gf, of)
+                for a, b in zip(go, oo):
+                    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        # one shared polyline, many lookahead distances, incl. exact hits of the cumulative length (strict '>')
+        sx = np.arange(P, dtype=np.float32) * np.float32(0.125); z = np.zeros(P, dtype=np.float32)
+        d = np.concatenate([np.arange(0, 70, dtype=np.float32) * np.float32(0.125), rng.uniform(-1, 9, 500).astype(np.float32)])
+        gi, gf, go = eng.extract_points(sx, z, z + 1, z, z + 2, d)
+        oi, of, oo = oracle.extract(sx, z, z + 1, z, z + 2, d)
+        assert np.array_equal(gi, oi) and np.array_equal(gf, of)
+        for a, b in zip(go, oo):
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        # empty trajectory: default point (d,0),(1,0),0 with idx -1
+        gi, gf, go = eng.extract_points(z[:0], z[:0], z[:0], z[:0], z[:0], np.float32([0.7]))
+        assert gi[0] == -1 and gf[0] == 2 and go[0][0] == np.float32(0.7) and go[2][0] == 1.0

@@ -1,0 +1,224 @@
+// libbmpc.so — C ABI part 1: errors, lifetime, model, options.  See include/bmpc.h for the contract.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "bmpc_internal.h"
+#include "shapes.h"
+
+namespace bmpc {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+int fail_cuda(cudaError_t e, const char* what)
+{
+    g_last_error = std::string("CUDA error '") + cudaGetErrorString(e) + "' in " + what;
+    cudaGetLastError();   // clear the sticky-less error state
+    return e == cudaErrorMemoryAllocation ? BMPC_E_NOMEM : BMPC_E_CUDA;
+}
+
+cudaError_t DevBuf::reserve(size_t n)
+{
+    if (n <= bytes) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e == cudaSuccess) bytes = n; else p = nullptr;
+    return e;
+}
+cudaError_t DevBuf::alloc_zero(size_t n, cudaStream_t st)
+{
+    cudaError_t e = reserve(n);
+    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(p, 0, n, st);
+}
+void DevBuf::release()
+{
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+}
+
+#define X(s, i, n) extern const ShapeOps bmpc_ops_##s##_##i##_##n;
+BMPC_SHAPES(X)
+#undef X
+
+const ShapeOps* find_shape(int S, int I, int N)
+{
+#define X(s, i, n) if (S == s && I == i && N == n) return &bmpc_ops_##s##_##i##_##n;
+    BMPC_SHAPES(X)
+#undef X
+    return nullptr;
+}
+
+}  // namespace bmpc
+
+using namespace bmpc;
+
+extern "C" {
+
+const char* bmpc_last_error(void) { return g_last_error.c_str(); }
+const char* bmpc_version(void) { return "bmpc 0.1 sm_100a (batched dlib::mpc-compatible linear MPC, CUDA)"; }
+int bmpc_shape_supported(int S, int I, int N) { return find_shape(S, I, N) != nullptr; }
+
+int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precision, int mode, int device)
+{
+    if (!out) return fail(BMPC_E_INVALID, "bmpc_create: out is null");
+    *out = nullptr;
+    if (capacity < 1) return fail(BMPC_E_INVALID, "bmpc_create: capacity must be >= 1");
+    if (precision != BMPC_FP64 && precision != BMPC_FP32) return fail(BMPC_E_UNSUPPORTED, "bmpc_create: precision must be 64 or 32");
+    if (mode != BMPC_MODE_EXACT && mode != BMPC_MODE_FAST) return fail(BMPC_E_UNSUPPORTED, "bmpc_create: unknown mode");
+    const ShapeOps* ops = find_shape(S, I, N);
+    if (!ops) {
+        char b[160];
+        snprintf(b, sizeof b, "bmpc_create: shape (S=%d,I=%d,N=%d) is not instantiated in this build (see csrc/shapes.h)", S, I, N);
+        return fail(BMPC_E_UNSUPPORTED, b);
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(BMPC_E_CUDA, "bmpc_create: no CUDA device available (this engine has no CPU fallback)");
+    }
+    if (device < 0) BMPC_CUDA(cudaGetDevice(&device));
+    if (device >= ndev) return fail(BMPC_E_INVALID, "bmpc_create: device index out of range");
+    BMPC_CUDA(cudaSetDevice(device));
+
+    bmpc_handle* h = new (std::nothrow) bmpc_handle();
+    if (!h) return fail(BMPC_E_NOMEM, "bmpc_create: out of host memory");
+    h->S = S; h->I = I; h->N = N; h->NI = N * I;
+    h->precision = precision; h->mode = mode; h->device = device;
+    h->elem = precision == BMPC_FP64 ? 8 : 4;
+    h->cap = capacity; h->ops = ops;
+    int rc = BMPC_OK;
+    auto chk = [&](cudaError_t ce, const char* what) { if (rc == BMPC_OK && ce != cudaSuccess) rc = fail_cuda(ce, what); };
+    chk(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
+    chk(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    chk(cudaEventCreate(&h->ev0), "cudaEventCreate");
+    chk(cudaEventCreate(&h->ev1), "cudaEventCreate");
+    const size_t c = (size_t)capacity, es = (size_t)h->elem;
+    chk(h->x0.alloc_zero(c * S * es, h->stream), "alloc x0");
+    chk(h->u0.alloc_zero(c * I * es, h->stream), "alloc u0");
+    chk(h->iters.alloc_zero(c * 4, h->stream), "alloc iters");
+    chk(h->status.alloc_zero(c, h->stream), "alloc status");
+    chk(h->controls.alloc_zero(c * h->NI * es, h->stream), "alloc controls");
+    chk(h->vstate.alloc_zero(c * h->NI * es, h->stream), "alloc v");
+    chk(h->target_const.alloc_zero(c * S * es, h->stream), "alloc target");
+    chk(h->queue.alloc_zero(64, h->stream), "alloc queue");
+    chk(h->small.alloc_zero(8 * 4096, h->stream), "alloc small");
+    h->pinned_bytes = 8 * 4096;
+    chk(cudaHostAlloc(&h->pinned, h->pinned_bytes, cudaHostAllocDefault), "cudaHostAlloc");
+    chk(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    if (rc != BMPC_OK) { std::string keep = g_last_error; bmpc_destroy(h); g_last_error = keep; return rc; }
+    *out = h;
+    return BMPC_OK;
+}
+
+void bmpc_destroy(bmpc_t* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
+                      &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
+                      &h->stage, &h->small};
+    for (DevBuf* b : bufs) b->release();
+    for (DevBuf& b : h->ex) b.release();
+    if (h->pinned) cudaFreeHost(h->pinned);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int bmpc_set_options(bmpc_t* h, double eps, uint64_t max_iterations)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_set_options: null handle");
+    if (!(eps > 0)) return fail(BMPC_E_INVALID, "bmpc_set_options: eps must be > 0 (mpc.h:203 requires)");
+    h->eps = eps;
+    h->max_iter = max_iterations > 0xffffffffull ? 0xffffffffu : (uint32_t)max_iterations;
+    return BMPC_OK;
+}
+int bmpc_get_options(bmpc_t* h, double* eps, uint64_t* max_iterations)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_get_options: null handle");
+    if (eps) *eps = h->eps;
+    if (max_iterations) *max_iterations = h->max_iter;
+    return BMPC_OK;
+}
+
+// Upload `count` instance-major double vectors of length len and store them as [len][cap] of T.
+static int upload_soa(bmpc_t* h, const double* host, long long count, int len, DevBuf& dst)
+{
+    const size_t bytes = (size_t)count * len * 8;
+    BMPC_CUDA(h->stage.reserve(bytes));
+    BMPC_CUDA(dst.reserve((size_t)h->cap * len * h->elem));
+    BMPC_CUDA(cudaMemcpyAsync(h->stage.p, host, bytes, cudaMemcpyHostToDevice, h->stream));
+    BMPC_CUDA(aos_to_soa((const double*)h->stage.p, dst.p, count, len, h->cap, h->elem, h->stream));
+    h->launches++;
+    // the staging buffer is reused by the next upload: wait (uploads are not on the solve hot path)
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C, const double* Q, const double* R,
+                   const double* lower, const double* upper, int per_instance, int64_t count)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_set_model: null handle");
+    if (!A || !B || !C || !Q || !R || !lower || !upper) return fail(BMPC_E_INVALID, "bmpc_set_model: null matrix pointer");
+    const int S = h->S, I = h->I, N = h->N;
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const long long cnt = per_instance ? count : 1;
+    if (cnt < 1 || cnt > h->cap) return fail(BMPC_E_INVALID, "bmpc_set_model: count out of range");
+    int rc;
+    if ((rc = upload_soa(h, A, cnt, S * S, h->mA)) || (rc = upload_soa(h, B, cnt, S * I, h->mB)) ||
+        (rc = upload_soa(h, C, cnt, S, h->mC)) || (rc = upload_soa(h, Q, cnt, S, h->mQ)) ||
+        (rc = upload_soa(h, R, cnt, I, h->mR)) || (rc = upload_soa(h, lower, cnt, I, h->mlo)) ||
+        (rc = upload_soa(h, upper, cnt, I, h->mhi)))
+        return rc;
+    BMPC_CUDA(h->mlambda.reserve((size_t)h->cap * h->elem));
+    BMPC_CUDA(h->mqdiag.reserve((size_t)h->cap * h->NI * h->elem));
+    GenericCtor g{cnt, h->cap, h->mA.p, h->mB.p, h->mQ.p, h->mR.p, h->mlambda.p, h->mqdiag.p};
+    BMPC_CUDA(h->ops->ctor(h->precision, h->mode, g, h->stream));   // mpc.h:114-123 on the device
+    h->launches++;
+    h->per_instance = per_instance != 0;
+    h->model_count = cnt;
+    if (!per_instance) {
+        // Keep the shared model on the host, rounded to the compute type, for the kernel-parameter block; read the
+        // device-computed lambda / Q_diag back (a few hundred bytes).
+        auto rnd = [&](const double* src, int n, std::vector<double>& dst) {
+            dst.resize(n);
+            for (int k = 0; k < n; ++k) dst[k] = h->elem == 8 ? src[k] : (double)(float)src[k];
+        };
+        rnd(A, S * S, h->hA); rnd(B, S * I, h->hB); rnd(C, S, h->hC); rnd(Q, S, h->hQ);
+        rnd(R, I, h->hR); rnd(lower, I, h->hlo); rnd(upper, I, h->hhi);
+        h->hqdiag.resize(h->NI);
+        int r2 = bmpc_get_derived(h, 0, &h->hlambda, h->hqdiag.data());
+        if (r2) return r2;
+    } else {
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->have_model = true;
+    (void)N;
+    return BMPC_OK;
+}
+
+int bmpc_get_derived(bmpc_t* h, int64_t instance, double* lambda, double* q_diag)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_get_derived: null handle");
+    if (!h->mlambda.p) return fail(BMPC_E_STATE, "bmpc_get_derived: no model set");
+    if (instance < 0 || instance >= h->cap) return fail(BMPC_E_INVALID, "bmpc_get_derived: instance out of range");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const int es = h->elem;
+    unsigned char* pin = (unsigned char*)h->pinned;
+    BMPC_CUDA(cudaMemcpyAsync(pin, (char*)h->mlambda.p + instance * es, es, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaMemcpy2DAsync(pin + 8, es, (char*)h->mqdiag.p + instance * es, (size_t)h->cap * es, es, h->NI,
+                                cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    if (lambda) *lambda = es == 8 ? ((double*)pin)[0] : (double)((float*)pin)[0];
+    if (q_diag)
+        for (int k = 0; k < h->NI; ++k) q_diag[k] = es == 8 ? ((double*)(pin + 8))[k] : (double)((float*)(pin + 8))[k];
+    return BMPC_OK;
+}
+
+}  // extern "C"

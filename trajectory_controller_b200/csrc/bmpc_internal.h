@@ -1,0 +1,86 @@
+// Internal definitions of libbmpc.so (host side): handle layout, error plumbing, generic layout kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/bmpc.h"
+#include "arith.cuh"
+#include "dispatch.h"
+
+namespace bmpc {
+
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+int fail_cuda(cudaError_t e, const char* what);
+
+#define BMPC_CUDA(call)                                                  \
+    do {                                                                 \
+        cudaError_t e__ = (call);                                        \
+        if (e__ != cudaSuccess) return ::bmpc::fail_cuda(e__, #call);    \
+    } while (0)
+
+// A growable device buffer (bytes).
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t n);
+    cudaError_t alloc_zero(size_t n, cudaStream_t st);
+    void release();
+};
+
+// Layout helpers (layout_kernels.cu).  AoS = instance-major host layout [count][len] of doubles;
+// SoA = device layout [len][stride] of T (T = double or float, selected by elem_size 8 / 4).
+cudaError_t aos_to_soa(const double* d_aos, void* d_soa, long long count, int len, long long stride, int elem_size,
+                       cudaStream_t st);
+cudaError_t soa_to_aos(const void* d_soa, double* d_aos, long long count, int len, long long stride, int elem_size,
+                       cudaStream_t st);
+// Broadcast one host vector of `len` doubles (passed by value through a small device buffer) into [len][stride].
+cudaError_t broadcast_rows(const double* d_vec, void* d_soa, long long count, int len, long long stride, int elem_size,
+                           cudaStream_t st);
+cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const float* px, const float* py,
+                           const float* dx, const float* dy, const float* vel, long long stride_instance,
+                           long long stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* opx,
+                           float* opy, float* odx, float* ody, float* ovel, cudaStream_t st);
+
+const ShapeOps* find_shape(int S, int I, int N);
+
+}  // namespace bmpc
+
+struct bmpc_handle {
+    int S, I, N, NI;
+    int precision, mode, device;
+    int elem;                     // sizeof(T)
+    long long cap;
+    const bmpc::ShapeOps* ops;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    int sm_count = 0;
+    int64_t launches = 0;
+
+    // options (mpc.h:103-104)
+    double eps = 0.01;
+    uint32_t max_iter = 10000;
+
+    // model
+    bool have_model = false, per_instance = false;
+    long long model_count = 0;
+    std::vector<double> hA, hB, hC, hQ, hR, hlo, hhi, hqdiag;   // shared model (host copies, already rounded to T)
+    double hlambda = 0;
+    bmpc::DevBuf mA, mB, mC, mQ, mR, mlo, mhi, mlambda, mqdiag;  // SoA [elem][cap]
+
+    // state
+    bmpc::DevBuf x0, u0, iters, status, controls, vstate, target_const, target_full, queue;
+    bool full_targets = false;
+    int head = 0;
+
+    // staging
+    bmpc::DevBuf stage;           // device, doubles in host (AoS) layout
+    bmpc::DevBuf small;           // device, a few hundred doubles
+    void* pinned = nullptr;       // host pinned mirror for small transfers
+    size_t pinned_bytes = 0;
+    bmpc::DevBuf ex[16];          // trajectory-point extraction buffers
+};

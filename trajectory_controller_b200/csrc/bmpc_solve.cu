@@ -1,0 +1,275 @@
+// libbmpc.so — C ABI part 2: targets, controller state, solve, trajectory-point extraction.
+#include <cstring>
+
+#include "bmpc_internal.h"
+
+using namespace bmpc;
+
+namespace {
+
+// Physical ring slot of horizon step `time` (targets shift by one per warm solve, mpc.h:236-237).
+inline int slot_of(const bmpc_handle* h, int time) { int s = h->head + time; return s >= h->N ? s - h->N : s; }
+
+int ensure_full_targets(bmpc_handle* h)
+{
+    if (h->full_targets) return BMPC_OK;
+    const size_t row = (size_t)h->cap * h->S * h->elem;
+    BMPC_CUDA(h->target_full.reserve(row * h->N));
+    for (int t = 0; t < h->N; ++t)   // every horizon step starts as the constant target
+        BMPC_CUDA(cudaMemcpyAsync((char*)h->target_full.p + row * t, h->target_const.p, row, cudaMemcpyDeviceToDevice, h->stream));
+    h->full_targets = true;
+    h->head = 0;
+    return BMPC_OK;
+}
+
+int write_target_rows(bmpc_handle* h, void* dst_rows, const double* val, int per_instance, long long count)
+{
+    const int S = h->S;
+    if (per_instance) {
+        const size_t bytes = (size_t)count * S * 8;
+        BMPC_CUDA(h->stage.reserve(bytes));
+        BMPC_CUDA(cudaMemcpyAsync(h->stage.p, val, bytes, cudaMemcpyHostToDevice, h->stream));
+        BMPC_CUDA(aos_to_soa((const double*)h->stage.p, dst_rows, count, S, h->cap, h->elem, h->stream));
+    } else {
+        std::memcpy(h->pinned, val, (size_t)S * 8);
+        BMPC_CUDA(cudaMemcpyAsync(h->small.p, h->pinned, (size_t)S * 8, cudaMemcpyHostToDevice, h->stream));
+        BMPC_CUDA(broadcast_rows((const double*)h->small.p, dst_rows, h->cap, S, h->cap, h->elem, h->stream));
+    }
+    h->launches++;
+    return BMPC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bmpc_set_target(bmpc_t* h, const double* val, int time, int per_instance, int64_t count)
+{
+    if (!h || !val) return fail(BMPC_E_INVALID, "bmpc_set_target: null argument");
+    if (time < -1 || time >= h->N) return fail(BMPC_E_INVALID, "bmpc_set_target: time must be -1 or < horizon (mpc.h:146 requires)");
+    if (per_instance && (count < 1 || count > h->cap)) return fail(BMPC_E_INVALID, "bmpc_set_target: count out of range");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t row = (size_t)h->cap * h->S * h->elem;
+    int rc;
+    if (time < 0) {                                           // set_target(val): every horizon step (mpc.h:157-163)
+        if ((rc = write_target_rows(h, h->target_const.p, val, per_instance, count))) return rc;
+        if (h->full_targets)
+            for (int t = 0; t < h->N; ++t) {
+                if (per_instance)   // only `count` instances change: row-wise 2D copy of the first `count` columns
+                    BMPC_CUDA(cudaMemcpy2DAsync((char*)h->target_full.p + row * t, (size_t)h->cap * h->elem, h->target_const.p,
+                                                (size_t)h->cap * h->elem, (size_t)count * h->elem, h->S,
+                                                cudaMemcpyDeviceToDevice, h->stream));
+                else
+                    BMPC_CUDA(cudaMemcpyAsync((char*)h->target_full.p + row * t, h->target_const.p, row, cudaMemcpyDeviceToDevice, h->stream));
+            }
+    } else {                                                  // set_target(val, time) (mpc.h:142-155)
+        if ((rc = ensure_full_targets(h))) return rc;
+        if ((rc = write_target_rows(h, (char*)h->target_full.p + row * slot_of(h, time), val, per_instance, count))) return rc;
+    }
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));               // `val` and the staging buffers are free again
+    return BMPC_OK;
+}
+
+int bmpc_get_target(bmpc_t* h, int64_t instance, int time, double* val)
+{
+    if (!h || !val) return fail(BMPC_E_INVALID, "bmpc_get_target: null argument");
+    if (time < 0 || time >= h->N) return fail(BMPC_E_INVALID, "bmpc_get_target: time must be < horizon (mpc.h:133 requires)");
+    if (instance < 0 || instance >= h->cap) return fail(BMPC_E_INVALID, "bmpc_get_target: instance out of range");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const int es = h->elem;
+    const size_t row = (size_t)h->cap * h->S * es;
+    const char* base = h->full_targets ? (const char*)h->target_full.p + row * slot_of(h, time) : (const char*)h->target_const.p;
+    BMPC_CUDA(cudaMemcpy2DAsync(h->pinned, es, base + instance * es, (size_t)h->cap * es, es, h->S, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < h->S; ++r) val[r] = es == 8 ? ((double*)h->pinned)[r] : (double)((float*)h->pinned)[r];
+    return BMPC_OK;
+}
+
+int bmpc_reset(bmpc_t* h)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_reset: null handle");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(cudaMemsetAsync(h->controls.p, 0, h->controls.bytes, h->stream));
+    BMPC_CUDA(cudaMemsetAsync(h->vstate.p, 0, h->vstate.bytes, h->stream));
+    BMPC_CUDA(cudaMemsetAsync(h->target_const.p, 0, h->target_const.bytes, h->stream));
+    if (h->full_targets) BMPC_CUDA(cudaMemsetAsync(h->target_full.p, 0, h->target_full.bytes, h->stream));
+    h->head = 0;
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_get_controls(bmpc_t* h, int64_t first, int64_t count, double* controls)
+{
+    if (!h || !controls) return fail(BMPC_E_INVALID, "bmpc_get_controls: null argument");
+    if (first < 0 || count < 1 || first + count > h->cap) return fail(BMPC_E_INVALID, "bmpc_get_controls: range out of capacity");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)count * h->NI * 8;
+    BMPC_CUDA(h->stage.reserve(bytes));
+    BMPC_CUDA(soa_to_aos((const char*)h->controls.p + first * h->elem, (double*)h->stage.p, count, h->NI, h->cap, h->elem, h->stream));
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(controls, h->stage.p, bytes, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_set_controls(bmpc_t* h, int64_t first, int64_t count, const double* controls)
+{
+    if (!h || !controls) return fail(BMPC_E_INVALID, "bmpc_set_controls: null argument");
+    if (first < 0 || count < 1 || first + count > h->cap) return fail(BMPC_E_INVALID, "bmpc_set_controls: range out of capacity");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)count * h->NI * 8;
+    BMPC_CUDA(h->stage.reserve(bytes));
+    BMPC_CUDA(cudaMemcpyAsync(h->stage.p, controls, bytes, cudaMemcpyHostToDevice, h->stream));
+    BMPC_CUDA(aos_to_soa((const double*)h->stage.p, (char*)h->controls.p + first * h->elem, count, h->NI, h->cap, h->elem, h->stream));
+    h->launches++;
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
+{
+    if (!h || !x0) return fail(BMPC_E_INVALID, "bmpc_upload_x0: null argument");
+    if (count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_upload_x0: count out of capacity");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)count * h->S * 8;
+    BMPC_CUDA(h->stage.reserve(bytes + (size_t)count * h->I * 8));
+    BMPC_CUDA(cudaMemcpyAsync(h->stage.p, x0, bytes, cudaMemcpyHostToDevice, h->stream));
+    BMPC_CUDA(aos_to_soa((const double*)h->stage.p, h->x0.p, count, h->S, h->cap, h->elem, h->stream));
+    h->launches++;
+    return BMPC_OK;
+}
+
+int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_solve: null handle");
+    if (!h->have_model) return fail(BMPC_E_STATE, "bmpc_solve: bmpc_set_model has not been called");
+    if (count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_solve: count out of capacity");
+    if (h->per_instance && count > h->model_count) return fail(BMPC_E_INVALID, "bmpc_solve: more instances than per-instance models");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const bool warm = (flags & BMPC_WARM) != 0;
+    GenericSolve g{};
+    g.A = h->hA.data(); g.B = h->hB.data(); g.C = h->hC.data(); g.Q = h->hQ.data(); g.R = h->hR.data();
+    g.lo = h->hlo.data(); g.hi = h->hhi.data(); g.lambda = h->hlambda; g.qdiag = h->hqdiag.data();
+    g.eps = h->eps; g.max_iter = h->max_iter;
+    g.warm = warm; g.keep_controls = warm || (flags & BMPC_KEEP_CONTROLS);
+    g.target_full = h->full_targets; g.head = h->head;
+    g.count = count; g.stride = h->cap;
+    g.x0 = h->x0.p; g.controls = h->controls.p; g.vstate = h->vstate.p;
+    g.target = h->full_targets ? h->target_full.p : h->target_const.p;
+    g.u0 = h->u0.p; g.iters = (uint32_t*)h->iters.p; g.status = (uint8_t*)h->status.p;
+    g.mA = h->mA.p; g.mB = h->mB.p; g.mC = h->mC.p; g.mQ = h->mQ.p; g.mR = h->mR.p; g.mlo = h->mlo.p; g.mhi = h->mhi.p;
+    g.mlambda = h->mlambda.p; g.mqdiag = h->mqdiag.p;
+    g.queue = (unsigned long long*)h->queue.p;
+    BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 8, h->stream));
+    BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
+    KernelInfo ki;
+    BMPC_CUDA(h->ops->info(h->precision, h->mode, h->per_instance, &ki));
+    // persistent grid: one CTA per SM, never more CTAs than there are warps' worth of instances
+    long long need_ctas = (count + ki.block - 1) / ki.block;
+    int grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
+    BMPC_CUDA(h->ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
+    BMPC_CUDA(cudaEventRecord(h->ev1, h->stream));
+    h->timed = true;
+    h->launches++;
+    if (warm && h->full_targets) h->head = h->head + 1 == h->N ? 0 : h->head + 1;   // mpc.h:236-237
+    return BMPC_OK;
+}
+
+int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t* status)
+{
+    if (!h || !u0) return fail(BMPC_E_INVALID, "bmpc_download: null argument");
+    if (count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_download: count out of capacity");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t off = (size_t)count * h->S * 8, bytes = (size_t)count * h->I * 8;
+    BMPC_CUDA(h->stage.reserve(off + bytes));
+    double* d_out = (double*)((char*)h->stage.p + off);
+    BMPC_CUDA(soa_to_aos(h->u0.p, d_out, count, h->I, h->cap, h->elem, h->stream));
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(u0, d_out, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (iters) BMPC_CUDA(cudaMemcpyAsync(iters, h->iters.p, (size_t)count * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (status) BMPC_CUDA(cudaMemcpyAsync(status, h->status.p, (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_solve(bmpc_t* h, int64_t count, const double* x0, double* u0, uint32_t* iters, uint8_t* status, unsigned flags)
+{
+    int rc;
+    if ((rc = bmpc_upload_x0(h, count, x0))) return rc;
+    if ((rc = bmpc_solve_resident_async(h, count, flags))) return rc;
+    return bmpc_download(h, count, u0, iters, status);
+}
+
+int bmpc_sync(bmpc_t* h)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_sync: null handle");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_last_kernel_ms(bmpc_t* h, float* ms)
+{
+    if (!h || !ms) return fail(BMPC_E_INVALID, "bmpc_last_kernel_ms: null argument");
+    if (!h->timed) return fail(BMPC_E_STATE, "bmpc_last_kernel_ms: no solve launched yet");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(cudaEventSynchronize(h->ev1));
+    BMPC_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return BMPC_OK;
+}
+
+int64_t bmpc_launch_count(bmpc_t* h) { return h ? h->launches : 0; }
+
+int bmpc_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* regs)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_kernel_info: null handle");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    KernelInfo ki;
+    BMPC_CUDA(h->ops->info(h->precision, h->mode, h->per_instance, &ki));
+    if (grid) *grid = h->sm_count;
+    if (block) *block = ki.block;
+    if (smem_bytes) *smem_bytes = ki.smem_bytes;
+    if (regs) *regs = ki.regs;
+    return BMPC_OK;
+}
+
+int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints, const float* px, const float* py,
+                        const float* dx, const float* dy, const float* vel, int64_t stride_instance,
+                        int64_t stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* out_px,
+                        float* out_py, float* out_dx, float* out_dy, float* out_vel)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_extract_points: null handle");
+    if (count < 1 || P < 0 || !dist || !idx || !flag || !out_px || !out_py || !out_dx || !out_dy || !out_vel)
+        return fail(BMPC_E_INVALID, "bmpc_extract_points: bad argument");
+    if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, "bmpc_extract_points: null trajectory array");
+    if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, "bmpc_extract_points: negative stride");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t nflt = P > 0 ? (size_t)((count - 1) * stride_instance + (int64_t)(P - 1) * stride_point + 1) : 0;
+    const float* src[5] = {px, py, dx, dy, vel};
+    for (int a = 0; a < 5; ++a) {
+        BMPC_CUDA(h->ex[a].reserve(nflt * 4 + 4));
+        if (nflt) BMPC_CUDA(cudaMemcpyAsync(h->ex[a].p, src[a], nflt * 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    BMPC_CUDA(h->ex[5].reserve((size_t)count * 4));
+    BMPC_CUDA(cudaMemcpyAsync(h->ex[5].p, dist, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    if (npoints) {
+        BMPC_CUDA(h->ex[6].reserve((size_t)count * 4));
+        BMPC_CUDA(cudaMemcpyAsync(h->ex[6].p, npoints, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    for (int a = 7; a < 14; ++a) BMPC_CUDA(h->ex[a].reserve((size_t)count * 4));
+    BMPC_CUDA(launch_extract(count, P, npoints ? (const int32_t*)h->ex[6].p : nullptr, (const float*)h->ex[0].p,
+                             (const float*)h->ex[1].p, (const float*)h->ex[2].p, (const float*)h->ex[3].p,
+                             (const float*)h->ex[4].p, stride_instance, stride_point, (const float*)h->ex[5].p,
+                             (int32_t*)h->ex[7].p, (uint8_t*)h->ex[8].p, (float*)h->ex[9].p, (float*)h->ex[10].p,
+                             (float*)h->ex[11].p, (float*)h->ex[12].p, (float*)h->ex[13].p, h->stream));
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(idx, h->ex[7].p, (size_t)count * 4, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaMemcpyAsync(flag, h->ex[8].p, (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    float* outs[5] = {out_px, out_py, out_dx, out_dy, out_vel};
+    for (int a = 0; a < 5; ++a)
+        BMPC_CUDA(cudaMemcpyAsync(outs[a], h->ex[9 + a].p, (size_t)count * 4, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+}  // extern "C"

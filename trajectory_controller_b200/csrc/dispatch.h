@@ -1,0 +1,40 @@
+// Host-side, shape-erased view of one template instantiation family (internal to libbmpc.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace bmpc {
+
+// Everything a solve launch needs, in doubles / untyped device pointers; the shape's translation unit converts it
+// into its SolveParams<T,S,I,N> kernel-parameter block.
+struct GenericSolve {
+    const double *A, *B, *C, *Q, *R, *lo, *hi;   // shared model (host), may be null for per-instance models
+    double lambda;
+    const double* qdiag;                         // host [N*I]
+    double eps;
+    uint32_t max_iter;
+    int warm, keep_controls, target_full, head;
+    long long count, stride;
+    const void* x0; void* controls; void* vstate; void* target; void* u0;
+    uint32_t* iters; uint8_t* status;
+    const void *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
+    unsigned long long* queue;
+};
+
+// mpc.h:114-123 for `count` models held SoA [elem][stride] on the device.
+struct GenericCtor {
+    long long count, stride;
+    const void *mA, *mB, *mQ, *mR;
+    void* mlambda; void* mqdiag;
+};
+
+struct KernelInfo { int block, smem_bytes, regs, warps, local_bytes; };
+
+struct ShapeOps {
+    int S, I, N;
+    cudaError_t (*solve)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
+    cudaError_t (*ctor)(int precision, int mode, const GenericCtor& g, cudaStream_t st);
+    cudaError_t (*info)(int precision, int mode, int pim, KernelInfo* out);
+};
+
+}  // namespace bmpc

@@ -1,0 +1,120 @@
+// Generic (shape-independent) device kernels of libbmpc.so:
+//  * layout changes between the ABI's instance-major double arrays and the engine's [element][instance] arrays
+//  * trajectory-point extraction, src/trajectory_point_follower.cpp:392-443
+#include "bmpc_internal.h"
+
+namespace bmpc {
+namespace {
+
+// One thread per (instance, element).  Reads are strided by `len` doubles (len <= 16 in practice, every byte of
+// a fetched sector is used by a neighbouring thread of the same warp via L1), writes are coalesced.
+template <typename T>
+__global__ void k_aos_to_soa(const double* __restrict__ in, T* __restrict__ out, long long count, int len, long long stride)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    for (int e = 0; e < len; ++e) out[(long long)e * stride + b] = (T)in[b * len + e];
+}
+template <typename T>
+__global__ void k_soa_to_aos(const T* __restrict__ in, double* __restrict__ out, long long count, int len, long long stride)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    for (int e = 0; e < len; ++e) out[b * len + e] = (double)in[(long long)e * stride + b];
+}
+template <typename T>
+__global__ void k_broadcast(const double* __restrict__ vec, T* __restrict__ out, long long count, int len, long long stride)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    for (int e = 0; e < len; ++e) out[(long long)e * stride + b] = (T)vec[e];
+}
+
+// getTrajectoryPoint's scan + interpolation (src/trajectory_point_follower.cpp:392-443), one thread per polyline.
+// The arc length is a SEQUENTIAL float sum (:423-427): a parallel scan would round differently and could flip the
+// selected index, so each thread walks its polyline in order; every float operation is rounded separately
+// (no FMA), matching the float semantics adopted for the un-vendored lms::math::vertex2f:
+// distance = sqrtf(ex*ex + ey*ey), normalize = (ex/len, ey/len), operator*(float), operator+.
+// With the point-major layout (stride_point = count, stride_instance = 1) every load is coalesced.
+__global__ void k_extract(long long count, int P, const int32_t* __restrict__ npoints, const float* __restrict__ px,
+                          const float* __restrict__ py, const float* __restrict__ dx, const float* __restrict__ dy,
+                          const float* __restrict__ vel, long long si, long long sp, const float* __restrict__ dist,
+                          int32_t* __restrict__ idx, uint8_t* __restrict__ flag, float* __restrict__ opx,
+                          float* __restrict__ opy, float* __restrict__ odx, float* __restrict__ ody,
+                          float* __restrict__ ovel)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    const float d = dist[b];
+    int n = npoints ? npoints[b] : P;
+    if (n > P) n = P;
+    const long long o = b * si;
+    float rx = d, ry = 0.0f, rdx = 1.0f, rdy = 0.0f, rv = 0.0f;     // :394-403 default point
+    int ri = -1; uint8_t rf = BMPC_PT_EMPTY;
+    if (n > 0) {                                                     // :404-407
+        float cur = 0.0f;                                            // :423
+        float bx = px[o], by = py[o];
+        bool found = false;
+        for (int i = 1; i < n; ++i) {                                // :424
+            const float tx = px[o + i * sp], ty = py[o + i * sp];
+            const float ex = __fsub_rn(bx, tx), ey = __fsub_rn(by, ty);
+            const float len = __fsqrt_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)));   // :427 distance()
+            cur = __fadd_rn(cur, len);
+            if (cur > d) {                                           // :428 strict
+                const float delta = __fsub_rn(cur, d);              // :431
+                const float ax = __fmul_rn(__fdiv_rn(ex, len), delta), ay = __fmul_rn(__fdiv_rn(ey, len), delta);   // :432
+                rx = __fadd_rn(tx, ax); ry = __fadd_rn(ty, ay);      // :433-434
+                rdx = dx[o + i * sp]; rdy = dy[o + i * sp]; rv = vel[o + i * sp];
+                ri = i; rf = BMPC_PT_INTERPOLATED; found = true;
+                break;                                               // :435-436
+            }
+            bx = tx; by = ty;
+        }
+        if (!found) {                                                // :439-442
+            const long long l = o + (long long)(n - 1) * sp;
+            rx = px[l]; ry = py[l]; rdx = dx[l]; rdy = dy[l]; rv = vel[l];
+            ri = n - 1; rf = BMPC_PT_LAST;
+        }
+    }
+    idx[b] = ri; flag[b] = rf; opx[b] = rx; opy[b] = ry; odx[b] = rdx; ody[b] = rdy; ovel[b] = rv;
+}
+
+inline unsigned blocks_for(long long count, int block) { return (unsigned)((count + block - 1) / block); }
+}  // namespace
+
+cudaError_t aos_to_soa(const double* d_aos, void* d_soa, long long count, int len, long long stride, int elem_size,
+                       cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    if (elem_size == 8) k_aos_to_soa<double><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (double*)d_soa, count, len, stride);
+    else k_aos_to_soa<float><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (float*)d_soa, count, len, stride);
+    return cudaGetLastError();
+}
+cudaError_t soa_to_aos(const void* d_soa, double* d_aos, long long count, int len, long long stride, int elem_size,
+                       cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    if (elem_size == 8) k_soa_to_aos<double><<<blocks_for(count, 256), 256, 0, st>>>((const double*)d_soa, d_aos, count, len, stride);
+    else k_soa_to_aos<float><<<blocks_for(count, 256), 256, 0, st>>>((const float*)d_soa, d_aos, count, len, stride);
+    return cudaGetLastError();
+}
+cudaError_t broadcast_rows(const double* d_vec, void* d_soa, long long count, int len, long long stride, int elem_size,
+                           cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    if (elem_size == 8) k_broadcast<double><<<blocks_for(count, 256), 256, 0, st>>>(d_vec, (double*)d_soa, count, len, stride);
+    else k_broadcast<float><<<blocks_for(count, 256), 256, 0, st>>>(d_vec, (float*)d_soa, count, len, stride);
+    return cudaGetLastError();
+}
+cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const float* px, const float* py,
+                           const float* dx, const float* dy, const float* vel, long long stride_instance,
+                           long long stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* opx,
+                           float* opy, float* odx, float* ody, float* ovel, cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    k_extract<<<blocks_for(count, 128), 128, 0, st>>>(count, P, npoints, px, py, dx, dy, vel, stride_instance,
+                                                     stride_point, dist, idx, flag, opx, opy, odx, ody, ovel);
+    return cudaGetLastError();
+}
+
+}  // namespace bmpc

@@ -1,0 +1,95 @@
+// One translation unit per template shape: nvcc ... -DBMPC_S=4 -DBMPC_I=1 -DBMPC_N=30 solve_inst.cu
+// Instantiates the solve kernel for {fp64,fp32} x {exact,fast} x {shared,per-instance model} and the constructor
+// kernel (mpc.h:114-123), and exports them through a shape-erased ShapeOps table (dispatch.h).
+#include "ctor_kernel.cuh"
+#include "dispatch.h"
+#include "solve_kernel.cuh"
+
+#ifndef BMPC_S
+#error "compile with -DBMPC_S= -DBMPC_I= -DBMPC_N="
+#endif
+
+namespace bmpc {
+namespace {
+constexpr int S_ = BMPC_S, I_ = BMPC_I, N_ = BMPC_N;
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
+{
+    using L = Layout<T, S_, I_, N_, PIM>;
+    SolveParams<T, S_, I_, N_> p;
+    for (int e = 0; e < S_ * S_; ++e) p.A[e] = PIM ? T(0) : (T)g.A[e];
+    for (int e = 0; e < S_ * I_; ++e) p.B[e] = PIM ? T(0) : (T)g.B[e];
+    for (int e = 0; e < S_; ++e) { p.C[e] = PIM ? T(0) : (T)g.C[e]; p.Q[e] = PIM ? T(0) : (T)g.Q[e]; }
+    for (int e = 0; e < I_; ++e) {
+        p.R[e] = PIM ? T(0) : (T)g.R[e]; p.lo[e] = PIM ? T(0) : (T)g.lo[e]; p.hi[e] = PIM ? T(0) : (T)g.hi[e];
+    }
+    p.lambda = PIM ? T(1) : (T)g.lambda;
+    for (int e = 0; e < N_ * I_; ++e) p.qdiag[e] = PIM ? T(0) : (T)g.qdiag[e];
+    p.eps = (T)g.eps; p.max_iter = g.max_iter;
+    p.warm = g.warm; p.keep_controls = g.keep_controls; p.target_full = g.target_full; p.head = g.head;
+    p.count = g.count; p.stride = g.stride;
+    p.x0 = (const T*)g.x0; p.controls = (T*)g.controls; p.vstate = (T*)g.vstate; p.target = (T*)g.target;
+    p.u0 = (T*)g.u0; p.iters = g.iters; p.status = g.status;
+    p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
+    p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
+    p.queue = g.queue;
+    auto kern = solve_kernel<T, S_, I_, N_, EXACT, PIM>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
+    return cudaGetLastError();
+}
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t info_solve(KernelInfo* out)
+{
+    using L = Layout<T, S_, I_, N_, PIM>;
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, solve_kernel<T, S_, I_, N_, EXACT, PIM>);
+    if (e != cudaSuccess) return e;
+    out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
+    out->local_bytes = (int)a.localSizeBytes;
+    return cudaSuccess;
+}
+
+template <typename T, bool EXACT>
+cudaError_t launch_ctor(const GenericCtor& g, cudaStream_t st)
+{
+    const int block = 128;
+    const long long grid = (g.count + block - 1) / block;
+    ctor_kernel<T, S_, I_, N_, EXACT><<<(unsigned)grid, block, 0, st>>>(
+        g.count, g.stride, (const T*)g.mA, (const T*)g.mB, (const T*)g.mQ, (const T*)g.mR, (T*)g.mlambda, (T*)g.mqdiag);
+    return cudaGetLastError();
+}
+
+#define BMPC_DISPATCH(FN, ...)                                                                                   \
+    do {                                                                                                         \
+        const bool ex = (mode == 0);                                                                             \
+        if (precision == 64) {                                                                                   \
+            if (ex) { if (pim) return FN<double, true, true>(__VA_ARGS__); return FN<double, true, false>(__VA_ARGS__); }   \
+            if (pim) return FN<double, false, true>(__VA_ARGS__);                                                \
+            return FN<double, false, false>(__VA_ARGS__);                                                        \
+        }                                                                                                        \
+        if (ex) { if (pim) return FN<float, true, true>(__VA_ARGS__); return FN<float, true, false>(__VA_ARGS__); }         \
+        if (pim) return FN<float, false, true>(__VA_ARGS__);                                                     \
+        return FN<float, false, false>(__VA_ARGS__);                                                             \
+    } while (0)
+
+cudaError_t solve_entry(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st)
+{ BMPC_DISPATCH(launch_solve, g, grid, st); }
+cudaError_t info_entry(int precision, int mode, int pim, KernelInfo* out)
+{ BMPC_DISPATCH(info_solve, out); }
+cudaError_t ctor_entry(int precision, int mode, const GenericCtor& g, cudaStream_t st)
+{
+    if (precision == 64) return mode == 0 ? launch_ctor<double, true>(g, st) : launch_ctor<double, false>(g, st);
+    return mode == 0 ? launch_ctor<float, true>(g, st) : launch_ctor<float, false>(g, st);
+}
+}  // namespace
+
+#define BMPC_CAT_(a, b, c) bmpc_ops_##a##_##b##_##c
+#define BMPC_CAT(a, b, c) BMPC_CAT_(a, b, c)
+extern const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N);
+const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N) = {S_, I_, N_, solve_entry, ctor_entry, info_entry};
+
+}  // namespace bmpc

@@ -1,0 +1,259 @@
+"""ctypes binding of the C-ABI product library ``libbmpc.so`` (include/bmpc.h).
+
+This is what a Python caller of the engine uses; tests and bench.py go through it, i.e. through the C ABI.
+There is no fallback of any kind: if the library is missing, not loadable, or no CUDA device is present, the
+calls raise.  Nothing in here imports or touches ``oracle/``.
+
+``BatchedMPC`` mirrors ``dlib::mpc<S,I,N>``'s method set (/root/reference/dlib_files/dlib/control/mpc.h:127-240)
+for a batch of controllers: ``set_target``, ``set_last_target``, ``get_target``, ``set_epsilon``,
+``set_max_iterations``, and ``__call__(x0)`` (= operator()) with the persistent-controller shift semantics.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbmpc.so")
+
+FP64, FP32 = 64, 32
+EXACT, FAST = 0, 1
+WARM, KEEP_CONTROLS = 1, 2
+ST_MAXITER = 1
+PT_INTERPOLATED, PT_LAST, PT_EMPTY = 0, 1, 2
+
+_dp = C.POINTER(C.c_double)
+_fp = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
+_u32p = C.POINTER(C.c_uint32)
+_u8p = C.POINTER(C.c_uint8)
+
+# name -> (restype, argtypes): every symbol include/bmpc.h declares
+SIGNATURES = {
+    "bmpc_shape_supported": (C.c_int, [C.c_int] * 3),
+    "bmpc_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int]),
+    "bmpc_destroy": (None, [C.c_void_p]),
+    "bmpc_last_error": (C.c_char_p, []),
+    "bmpc_version": (C.c_char_p, []),
+    "bmpc_set_model": (C.c_int, [C.c_void_p] + [_dp] * 7 + [C.c_int, C.c_int64]),
+    "bmpc_set_options": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64]),
+    "bmpc_get_options": (C.c_int, [C.c_void_p, _dp, C.POINTER(C.c_uint64)]),
+    "bmpc_get_derived": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp]),
+    "bmpc_set_target": (C.c_int, [C.c_void_p, _dp, C.c_int, C.c_int, C.c_int64]),
+    "bmpc_get_target": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _dp]),
+    "bmpc_reset": (C.c_int, [C.c_void_p]),
+    "bmpc_get_controls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, _dp]),
+    "bmpc_set_controls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, _dp]),
+    "bmpc_solve": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _u32p, _u8p, C.c_uint]),
+    "bmpc_upload_x0": (C.c_int, [C.c_void_p, C.c_int64, _dp]),
+    "bmpc_solve_resident_async": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint]),
+    "bmpc_download": (C.c_int, [C.c_void_p, C.c_int64, _dp, _u32p, _u8p]),
+    "bmpc_sync": (C.c_int, [C.c_void_p]),
+    "bmpc_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
+    "bmpc_launch_count": (C.c_int64, [C.c_void_p]),
+    "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
+    "bmpc_probe_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
+    "bmpc_extract_points": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
+}
+
+_lib = None
+
+
+class BmpcError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"bmpc error {code}: {msg}")
+        self.code = code
+
+
+def lib() -> C.CDLL:
+    """Load libbmpc.so (once).  Raises if it has not been built — there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                    "or `make -C trajectory_controller_b200/csrc -j8`")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise BmpcError(rc, lib().bmpc_last_error().decode())
+
+
+def _c64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _p(a, t=_dp):
+    return None if a is None else a.ctypes.data_as(t)
+
+
+def shape_supported(S: int, I: int, N: int) -> bool:
+    return bool(lib().bmpc_shape_supported(S, I, N))
+
+
+class BatchedMPC:
+    """`capacity` dlib::mpc<S,I,N>-compatible controllers on one GPU."""
+
+    def __init__(self, S: int, I: int, N: int, capacity: int, precision: int = FP64, mode: int = EXACT, device: int = -1):
+        self.S, self.I, self.N, self.capacity = S, I, N, int(capacity)
+        self.precision, self.mode = precision, mode
+        self._h = C.c_void_p()
+        _check(lib().bmpc_create(C.byref(self._h), S, I, N, self.capacity, precision, mode, device))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().bmpc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- model / options -----------------------------------------------------------------------------------------
+    def set_model(self, model, per_instance: bool = False):
+        g = (lambda k: model[k]) if isinstance(model, dict) else (lambda k: getattr(model, k))
+        arrs = [_c64(g(k)) for k in ("A", "B", "C", "Q", "R", "lower", "upper")]
+        count = arrs[0].shape[0] if per_instance else 1
+        _check(lib().bmpc_set_model(self._h, *[_p(a) for a in arrs], int(per_instance), count))
+        return self
+
+    def set_epsilon(self, eps: float):
+        _check(lib().bmpc_set_options(self._h, eps, self.get_max_iterations()))
+
+    def set_max_iterations(self, n: int):
+        _check(lib().bmpc_set_options(self._h, self.get_epsilon(), n))
+
+    def set_options(self, eps: float, max_iter: int):
+        _check(lib().bmpc_set_options(self._h, eps, max_iter))
+
+    def _opts(self):
+        e, m = C.c_double(), C.c_uint64()
+        _check(lib().bmpc_get_options(self._h, C.byref(e), C.byref(m)))
+        return e.value, m.value
+
+    def get_epsilon(self) -> float:
+        return self._opts()[0]
+
+    def get_max_iterations(self) -> int:
+        return self._opts()[1]
+
+    def derived(self, instance: int = 0):
+        lam = C.c_double(); qd = np.zeros((self.N, self.I))
+        _check(lib().bmpc_get_derived(self._h, instance, C.byref(lam), _p(qd)))
+        return lam.value, qd
+
+    # ---- targets ---------------------------------------------------------------------------------------------------
+    def set_target(self, val, time: int = -1):
+        """val: [S] (all instances) or [count][S].  time=-1: every horizon step (mpc.h:157-163)."""
+        v = _c64(val)
+        per = v.ndim == 2
+        _check(lib().bmpc_set_target(self._h, _p(v), time, int(per), v.shape[0] if per else 0))
+
+    def set_last_target(self, val):
+        self.set_target(val, self.N - 1)
+
+    def get_target(self, time: int, instance: int = 0):
+        out = np.zeros(self.S)
+        _check(lib().bmpc_get_target(self._h, instance, time, _p(out)))
+        return out
+
+    # ---- state --------------------------------------------------------------------------------------------------------
+    def reset(self):
+        _check(lib().bmpc_reset(self._h))
+
+    def get_controls(self, count: int | None = None, first: int = 0):
+        count = self.capacity - first if count is None else count
+        out = np.zeros((count, self.N, self.I))
+        _check(lib().bmpc_get_controls(self._h, first, count, _p(out)))
+        return out
+
+    def set_controls(self, controls, first: int = 0):
+        c = _c64(controls)
+        _check(lib().bmpc_set_controls(self._h, first, c.shape[0], _p(c)))
+
+    # ---- solve ----------------------------------------------------------------------------------------------------------
+    def solve(self, x0, warm: bool = False, keep_controls: bool = False, out=None):
+        """operator() for x0[count][S].  Returns (u0[count][I], iters[count] uint32, status[count] uint8)."""
+        x = _c64(x0)
+        B = x.shape[0]
+        if out is None:
+            u0 = np.empty((B, self.I)); it = np.empty(B, dtype=np.uint32); st = np.empty(B, dtype=np.uint8)
+        else:
+            u0, it, st = out
+        flags = (WARM if warm else 0) | (KEEP_CONTROLS if keep_controls else 0)
+        _check(lib().bmpc_solve(self._h, B, _p(x), _p(u0), _p(it, _u32p), _p(st, _u8p), flags))
+        return u0, it, st
+
+    __call__ = solve
+
+    def upload_x0(self, x0):
+        x = _c64(x0)
+        _check(lib().bmpc_upload_x0(self._h, x.shape[0], _p(x)))
+        return x.shape[0]
+
+    def solve_resident_async(self, count: int, warm: bool = False, keep_controls: bool = False):
+        _check(lib().bmpc_solve_resident_async(self._h, count, (WARM if warm else 0) | (KEEP_CONTROLS if keep_controls else 0)))
+
+    def download(self, count: int, out=None):
+        if out is None:
+            u0 = np.empty((count, self.I)); it = np.empty(count, dtype=np.uint32); st = np.empty(count, dtype=np.uint8)
+        else:
+            u0, it, st = out
+        _check(lib().bmpc_download(self._h, count, _p(u0), _p(it, _u32p), _p(st, _u8p)))
+        return u0, it, st
+
+    def sync(self):
+        _check(lib().bmpc_sync(self._h))
+
+    def last_kernel_ms(self) -> float:
+        ms = C.c_float()
+        _check(lib().bmpc_last_kernel_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self) -> int:
+        return int(lib().bmpc_launch_count(self._h))
+
+    def kernel_info(self):
+        g, b, s, r = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _check(lib().bmpc_kernel_info(self._h, C.byref(g), C.byref(b), C.byref(s), C.byref(r)))
+        return dict(grid=g.value, block=b.value, smem_bytes=s.value, regs=r.value)
+
+    def probe_peak(self, precision: int = FP64, fused: bool = True):
+        """(TFLOP/s, G instructions/s) of the device's FP64/FP32 pipe, measured with register-resident chains."""
+        t, g = C.c_double(), C.c_double()
+        _check(lib().bmpc_probe_peak(self._h, precision, int(fused), C.byref(t), C.byref(g)))
+        return t.value, g.value
+
+    # ---- trajectory point ---------------------------------------------------------------------------------------------------
+    def extract_points(self, px, py, dx, dy, vel, dist, npoints=None, layout: str = "shared"):
+        """getTrajectoryPoint for a batch.  layout 'shared': arrays [P] (one polyline for all); 'pb': [P][B]
+        point-major (coalesced on the device); 'bp': [B][P].  Returns (idx, flag, (px, py, dx, dy, vel))."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+        dist = np.ascontiguousarray(dist, dtype=np.float32)
+        B = dist.shape[0]
+        if layout == "shared":
+            P, si, sp = arrs[0].shape[0], 0, 1
+        elif layout == "pb":
+            P, si, sp = arrs[0].shape[0], 1, B
+        elif layout == "bp":
+            P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
+        else:
+            raise ValueError(layout)
+        npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+        idx = np.empty(B, dtype=np.int32); flag = np.empty(B, dtype=np.uint8)
+        outs = [np.empty(B, dtype=np.float32) for _ in range(5)]
+        _check(lib().bmpc_extract_points(self._h, B, P, _p(npts, _i32p), *[_p(a, _fp) for a in arrs], si, sp,
+                                         _p(dist, _fp), _p(idx, _i32p), _p(flag, _u8p), *[_p(o, _fp) for o in outs]))
+        return idx, flag, outs
