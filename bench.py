@@ -1,0 +1,312 @@
+#!/usr/bin/env python
+"""bench.py — MPC solves/sec of the batched dlib::mpc-compatible engine (BASELINE.json metric), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode exact|fast] [--precision 64|32]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1], SURVEY.md §8(d) "Config 2"): 65,536 independent cold dlib::mpc<4,1,30>
+controllers PER GPU (weak scaling: rank r draws its x0 with seed 42 + r), shared synthetic bicycle model, constant
+target 0, eps 0.01, max_iterations 10000, FP64.  One "step" = one operator() (mpc.h:216-240) for every instance
+of the batch.
+
+  value  : solves/s with x0 resident in HBM (kernel launches only), CUDA events on the launching stream, an L2 flush
+           (256 MiB memset) between timed steps, max over ranks.
+  e2e    : the same metric through the C ABI call bmpc_solve() with pinned HOST buffers (H2D of x0, layout change,
+           solve, D2H of u0 / iteration counts / status inside the timed region).
+  roofline: the solver is bound by the FP64 CUDA-core pipe; `achieved` = algorithmic flops
+           (F_setup + iters_i * F_iter summed over the instances one launch solves) / mean launch duration, `peak` = the
+           FP64 FMA peak measured on this device by bmpc_probe_peak (MEASURED_PEAKS.json has no FP64 figure).
+  cpu_baseline / --impl reference: the real dlib::mpc (oracle/_ref/libdlibref.so, built from the reference's own
+           header) or, if that library did not travel, the C restatement (oracle/liboracle.so) — one controller per
+           host thread on all host cores, on a bounded sample of the same instances.
+
+The product path is libbmpc.so only; oracle/ is touched by the CPU legs alone.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from trajectory_controller_b200 import workloads as W  # noqa: E402
+
+METRIC = "mpc_solves_per_sec_horizon30"
+UNIT = "solves/s"
+S_, I_, N_ = 4, 1, 30
+BATCH = 65536
+SEED = 42
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
+    ap.add_argument("--batch", type=int, default=BATCH, help="instances per GPU (default: the BASELINE config)")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    return ap.parse_args()
+
+
+def config_dict(args, world):
+    return {"workload": "configs[1]: 65,536 cold dlib::mpc<4,1,30> instances per GPU, random e_y/e_psi offsets "
+                        "(mt19937_64 seed 42+rank), shared bicycle4 model, target 0, eps 0.01, max_iter 10000",
+            "S": S_, "I": I_, "horizon": N_, "instances_per_gpu": args.batch, "global_instances": args.batch * world,
+            "precision": f"fp{args.precision}", "mode": args.mode, "sharding": f"instances x{world}",
+            "l2": "flushed between timed steps (256 MiB memset); the solver reads <5 MiB per step"}
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi SM clock + throttle reasons, sampled while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active"
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.maxmhz = index, threading.Event(), [], set(), None
+
+    def run(self):
+        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+                 0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+                 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.samples.append(float(f[0])); self.maxmhz = float(f[1])
+                bits = int(f[2], 16) if f[2].lower().startswith("0x") else 0
+                for b, n in names.items():
+                    if bits & b and n != "gpu_idle":
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.05)
+
+    def result(self):
+        self.stop_flag.set(); self.join(timeout=6)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.maxmhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------- CPU legs
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_solver():
+    """(kind, callable(model, N, x0, nthreads) -> seconds).  The one place bench.py executes oracle/."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _oracle import DlibRef, Oracle
+    if DlibRef.available():
+        ref = DlibRef()
+        if ref.supported(S_, I_, N_):
+            return "reference", lambda m, N, x0, nt: ref.batch_cold(m, N, x0, nthreads=nt, want_controls=False)[2]
+    orc = Oracle()
+    return "port", lambda m, N, x0, nt: orc.batch_cold(m, N, x0, nthreads=nt, want_controls=False)[3]
+
+
+def cpu_baseline(sample: int, seed: int):
+    kind, run = cpu_solver()
+    cores = host_cores()
+    x0 = W.random_offsets_x0(sample, seed)
+    secs = run(W.bicycle4_model(), N_, x0, cores)
+    return {"value": sample / secs, "unit": UNIT, "cores": cores, "kind": kind, "seconds": secs,
+            "sample": f"the first {sample} instances of rank 0's batch (seed {seed}), one cold dlib::mpc<4,1,30> per "
+                      f"instance, {cores} host threads over contiguous slices, g++ -O2 -ffp-contract=off"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU solver on this box's host cores; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = max(1, args.gpus)
+    kind, run = cpu_solver()
+    cores = host_cores()
+    sample = args.cpu_sample or 16384
+    x0 = W.random_offsets_x0(sample, SEED)
+    model = W.bicycle4_model()
+    for _ in range(args.warmup):
+        run(model, N_, x0[: max(cores * 8, 256)], cores)
+    t = 0.0
+    for _ in range(args.steps):
+        t += run(model, N_, x0, cores)
+    val = sample * args.steps / t
+    cfg = config_dict(args, world)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": f"each step = the first {sample} instances of the workload (seed {SEED}) on "
+                                       f"{cores} host threads, one cold dlib::mpc<4,1,30> per instance"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from trajectory_controller_b200.engine import EXACT, FAST, BatchedMPC
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the engine has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    B, K, Wm = args.batch, args.steps, max(args.warmup, 0)
+    mode = EXACT if args.mode == "exact" else FAST
+    model = W.bicycle4_model()
+    x0 = W.random_offsets_x0(B, SEED + rank)
+    # pinned host buffers for the end-to-end leg (numpy views of torch pinned tensors)
+    px0 = torch.empty((B, S_), dtype=torch.float64).pin_memory(); px0.numpy()[:] = x0
+    pu0 = torch.empty((B, I_), dtype=torch.float64).pin_memory()
+    pit = torch.empty(B, dtype=torch.int32).pin_memory()
+    pst = torch.empty(B, dtype=torch.uint8).pin_memory()
+    out = (pu0.numpy(), pit.numpy().view(np.uint32), pst.numpy())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+
+    eng = BatchedMPC(S_, I_, N_, B, args.precision, mode, device=local)
+    eng.set_model(model)
+    peak_tf, peak_gi = eng.probe_peak(args.precision, True)
+    _, peak_gi_unfused = eng.probe_peak(args.precision, False)
+    eng.set_stream(stream.cuda_stream)
+    info = eng.kernel_info()
+
+    with torch.cuda.stream(stream):
+        # ---------------- resident leg: x0 already in HBM --------------------------------------------------------
+        eng.upload_x0(px0.numpy())
+        for _ in range(Wm):
+            eng.solve_resident_async(B)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        barrier()
+        sampler = ClockSampler(local); sampler.start()
+        l0 = eng.launch_count()
+        for a, b in ev:
+            flush.zero_()
+            a.record(stream)
+            eng.solve_resident_async(B)
+            b.record(stream)
+        stream.synchronize()
+        launches = eng.launch_count() - l0
+        barrier()
+        step_ms = [a.elapsed_time(b) for a, b in ev]
+        t_res = max_over_ranks(sum(step_ms) / 1e3)
+        _, iters, status = eng.download(B, out)
+        iters = iters.astype(np.int64)
+
+        # ---------------- end-to-end leg: host buffers through bmpc_solve ------------------------------------------
+        for _ in range(min(Wm, 3)):
+            eng.solve(px0.numpy(), out=out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            eng.solve(px0.numpy(), out=out)
+        stream.synchronize()
+        t_e2e_local = time.perf_counter() - t0
+        barrier()
+        t_e2e = max_over_ranks(t_e2e_local)
+        clocks = sampler.result()
+
+        # ---------------- single-solve latency through the ABI (batch of 1, cold) ----------------------------------
+        lat = []
+        one = (np.empty((1, I_)), np.empty(1, dtype=np.uint32), np.empty(1, dtype=np.uint8))
+        for k in range(60):
+            t1 = time.perf_counter()
+            eng.solve(x0[k:k + 1], out=one)
+            lat.append(time.perf_counter() - t1)
+        lat = np.array(lat[10:]) * 1e6
+
+    flops = float(W.flops_setup(S_, I_, N_) * B + W.flops_per_iteration(S_, I_, N_) * iters.sum())
+    ms_launch = float(np.mean(step_ms))
+    achieved = flops / (ms_launch * 1e-3) / 1e12
+    total_units = B * world
+    value = total_units * K / t_res
+    e2e = total_units * K / t_e2e
+    mean_iters = sum_over_ranks(float(iters.mean())) / world
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": 1e3 * t_res / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic", "config": config_dict(args, world),
+            "clocks": clocks,
+            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / K, "h2d_bytes_per_step": B * S_ * 8,
+                    "d2h_bytes_per_step": B * (I_ * 8 + 4 + 1), "api": "bmpc_solve (C ABI, pinned host buffers)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe", "achieved": achieved, "peak": peak_tf,
+                         "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": None,
+                         "peak_source": "bmpc_probe_peak: register-resident FMA chains on this device (MEASURED_PEAKS.json "
+                                        "holds only HBM and bf16-tensor figures; the solver uses neither)",
+                         "peak_ginstr_fused": peak_gi, "peak_ginstr_unfused": peak_gi_unfused,
+                         "exact_mode_ceiling_frac": 0.5 if args.mode == "exact" else 1.0,
+                         "kernel": f"solve_kernel<{'double' if args.precision == 64 else 'float'},{S_},{I_},{N_},"
+                                   f"{'EXACT' if args.mode == 'exact' else 'FAST'},shared-model>",
+                         "kernel_ms": ms_launch, "algorithmic_flops_per_launch": flops,
+                         "hbm_bytes_per_launch_algorithmic": B * (S_ * 8 * 2 + I_ * 8 + 5),
+                         "launch": info},
+            "iterations": {"mean": mean_iters, "p50": float(np.percentile(iters, 50)), "p99": float(np.percentile(iters, 99)),
+                           "max": int(iters.max()), "hit_max_iterations": int((status != 0).sum())},
+            "latency_us_batch1": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                  "what": "one cold (4,1,30) solve through bmpc_solve incl. copies"}}
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED)
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -102,6 +102,10 @@ int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0);            /* H2
 int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags);   /* kernel only, on the handle's stream */
 int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t* status);
 int bmpc_sync(bmpc_t* h);
+/* Run every later call of this handle on the caller's CUDA stream (a cudaStream_t passed as void*; NULL = back to
+ * the handle's own stream).  Lets a host application order the engine with its own copies/events, and lets a
+ * benchmark bracket launches with its own events.  The handle never destroys a borrowed stream. */
+int bmpc_set_stream(bmpc_t* h, void* cuda_stream);
 /* CUDA-event time of the last solve kernel (ms), the number of kernels this handle has launched so far, and
  * the launch geometry of the solve kernel (for roofline bookkeeping). */
 int bmpc_last_kernel_ms(bmpc_t* h, float* ms);

@@ -93,7 +93,8 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     int rc = BMPC_OK;
     auto chk = [&](cudaError_t ce, const char* what) { if (rc == BMPC_OK && ce != cudaSuccess) rc = fail_cuda(ce, what); };
     chk(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
-    chk(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    chk(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    h->stream = h->own_stream;
     chk(cudaEventCreate(&h->ev0), "cudaEventCreate");
     chk(cudaEventCreate(&h->ev1), "cudaEventCreate");
     const size_t c = (size_t)capacity, es = (size_t)h->elem;
@@ -127,8 +128,18 @@ void bmpc_destroy(bmpc_t* h)
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
+}
+
+int bmpc_set_stream(bmpc_t* h, void* cuda_stream)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_set_stream: null handle");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));      // nothing of ours may still be in flight on the old stream
+    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+    h->timed = false;
+    return BMPC_OK;
 }
 
 int bmpc_set_options(bmpc_t* h, double eps, uint64_t max_iterations)

@@ -55,7 +55,8 @@ struct bmpc_handle {
     int elem;                     // sizeof(T)
     long long cap;
     const bmpc::ShapeOps* ops;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;       // the stream calls run on (own_stream unless bmpc_set_stream borrowed one)
+    cudaStream_t own_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     int sm_count = 0;

@@ -51,6 +51,7 @@ SIGNATURES = {
     "bmpc_solve_resident_async": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint]),
     "bmpc_download": (C.c_int, [C.c_void_p, C.c_int64, _dp, _u32p, _u8p]),
     "bmpc_sync": (C.c_int, [C.c_void_p]),
+    "bmpc_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bmpc_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
     "bmpc_launch_count": (C.c_int64, [C.c_void_p]),
     "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
@@ -216,6 +217,10 @@ class BatchedMPC:
 
     def sync(self):
         _check(lib().bmpc_sync(self._h))
+
+    def set_stream(self, cuda_stream: int | None):
+        """Borrow a caller's cudaStream_t (integer handle, e.g. torch.cuda.current_stream().cuda_stream); None/0 = own."""
+        _check(lib().bmpc_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
 
     def last_kernel_ms(self) -> float:
         ms = C.c_float()
