@@ -72,6 +72,13 @@ const char* bmpc_version(void);
  * 1: `count` models, instance-major.  Runs the lambda / Q_diag recursion (mpc.h:114-123) on the device. */
 int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C, const double* Q, const double* R,
                    const double* lower, const double* upper, int per_instance, int64_t count);
+/* Structural specialisation.  bmpc_set_model picks, among the kernels compiled for the shape, the one whose structural
+ * pattern (entries that are exactly 0 / exactly 1 in A, B, C, Q of EVERY instance) is the sparsest the model satisfies;
+ * dropping those terms is exact in IEEE arithmetic (only the sign of a zero can differ), so parity is unaffected.
+ * enable = 0 forces the dense kernel (takes effect at the next bmpc_set_model).  Default: enabled. */
+int bmpc_set_specialization(bmpc_t* h, int enable);
+/* Name of the pattern the current model runs with: "dense", "bicycle4", "tobi", "kat". */
+const char* bmpc_pattern_name(bmpc_t* h);
 /* mpc.h:190-214; defaults eps = 0.01, max_iterations = 10000 (mpc.h:103-104).  max_iterations saturates at 2^32-1. */
 int bmpc_set_options(bmpc_t* h, double eps, uint64_t max_iterations);
 int bmpc_get_options(bmpc_t* h, double* eps, uint64_t* max_iterations);

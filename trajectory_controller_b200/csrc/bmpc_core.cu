@@ -39,16 +39,57 @@ void DevBuf::release()
     p = nullptr; bytes = 0;
 }
 
-#define X(s, i, n) extern const ShapeOps bmpc_ops_##s##_##i##_##n;
+#define X(s, i, n, pt) extern const ShapeOps bmpc_ops_##s##_##i##_##n##_##pt;
 BMPC_SHAPES(X)
 #undef X
 
-const ShapeOps* find_shape(int S, int I, int N)
-{
-#define X(s, i, n) if (S == s && I == i && N == n) return &bmpc_ops_##s##_##i##_##n;
+static const ShapeOps* const g_all_ops[] = {
+#define X(s, i, n, pt) &bmpc_ops_##s##_##i##_##n##_##pt,
     BMPC_SHAPES(X)
 #undef X
+};
+
+// The dense instantiation of a shape: accepts every model, owns the constructor kernel.
+const ShapeOps* find_shape(int S, int I, int N)
+{
+    for (const ShapeOps* o : g_all_ops)
+        if (o->S == S && o->I == I && o->N == N && o->ctor && std::strcmp(o->pattern, "dense") == 0) return o;
     return nullptr;
+}
+
+static int popcount_u(unsigned x) { int n = 0; while (x) { n += x & 1u; x >>= 1; } return n; }
+
+// A model (count instances, instance-major doubles already rounded to the compute type by `rnd`) satisfies a pattern
+// iff every non-zero entry is allowed by the NZ bits and every ONE-bit entry equals exactly 1.
+static bool entries_fit(const double* v, long long count, int len, unsigned nz, unsigned one, bool as_float)
+{
+    for (long long b = 0; b < count; ++b)
+        for (int e = 0; e < len; ++e) {
+            double x = v[b * len + e];
+            if (as_float) x = (double)(float)x;
+            if (x != 0.0 && !((nz >> e) & 1u)) return false;
+            if (((one >> e) & 1u) && x != 1.0) return false;
+        }
+    return true;
+}
+
+// The sparsest compiled pattern of the shape that the model satisfies (the dense one always does).
+const ShapeOps* select_pattern(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
+                               long long count, bool as_float)
+{
+    const ShapeOps* best = nullptr;
+    int best_cost = 1 << 30;
+    for (const ShapeOps* o : g_all_ops) {
+        if (o->S != S || o->I != I || o->N != N) continue;
+        if (!entries_fit(A, count, S * S, o->anz, o->aone, as_float) || !entries_fit(B, count, S * I, o->bnz, o->bone, as_float) ||
+            !entries_fit(C, count, S, o->cnz, 0u, as_float) || !entries_fit(Q, count, S, o->qnz, 0u, as_float))
+            continue;
+        // cost ~ multiplications + additions per horizon step that survive
+        const int cost = 2 * (popcount_u(o->anz) * 2 - popcount_u(o->aone)) + 2 * (popcount_u(o->bnz) * 2 - popcount_u(o->bone)) +
+                         popcount_u(o->cnz) + 2 * popcount_u(o->qnz);
+        if (cost < best_cost) { best_cost = cost; best = o; }
+    }
+    return best;
 }
 
 }  // namespace bmpc
@@ -89,7 +130,7 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     h->S = S; h->I = I; h->N = N; h->NI = N * I;
     h->precision = precision; h->mode = mode; h->device = device;
     h->elem = precision == BMPC_FP64 ? 8 : 4;
-    h->cap = capacity; h->ops = ops;
+    h->cap = capacity; h->ops = ops; h->solve_ops = ops;
     int rc = BMPC_OK;
     auto chk = [&](cudaError_t ce, const char* what) { if (rc == BMPC_OK && ce != cudaSuccess) rc = fail_cuda(ce, what); };
     chk(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
@@ -141,6 +182,14 @@ int bmpc_set_stream(bmpc_t* h, void* cuda_stream)
     h->timed = false;
     return BMPC_OK;
 }
+
+int bmpc_set_specialization(bmpc_t* h, int enable)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_set_specialization: null handle");
+    h->specialize = enable != 0;
+    return BMPC_OK;
+}
+const char* bmpc_pattern_name(bmpc_t* h) { return h && h->solve_ops ? h->solve_ops->pattern : ""; }
 
 int bmpc_set_options(bmpc_t* h, double eps, uint64_t max_iterations)
 {
@@ -194,6 +243,8 @@ int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C,
     h->launches++;
     h->per_instance = per_instance != 0;
     h->model_count = cnt;
+    h->solve_ops = h->specialize ? select_pattern(S, I, N, A, B, C, Q, cnt, h->elem == 4) : h->ops;
+    if (!h->solve_ops) return fail(BMPC_E_UNSUPPORTED, "bmpc_set_model: no compiled pattern accepts this model (dense unit missing)");
     if (!per_instance) {
         // Keep the shared model on the host, rounded to the compute type, for the kernel-parameter block; read the
         // device-computed lambda / Q_diag back (a few hundred bytes).

@@ -46,6 +46,8 @@ cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const
                            float* opy, float* odx, float* ody, float* ovel, cudaStream_t st);
 
 const ShapeOps* find_shape(int S, int I, int N);
+const ShapeOps* select_pattern(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
+                               long long count, bool as_float);
 
 }  // namespace bmpc
 
@@ -54,7 +56,8 @@ struct bmpc_handle {
     int precision, mode, device;
     int elem;                     // sizeof(T)
     long long cap;
-    const bmpc::ShapeOps* ops;
+    const bmpc::ShapeOps* ops;         // dense unit of the shape (constructor kernel)
+    const bmpc::ShapeOps* solve_ops;   // pattern-specialised unit chosen by bmpc_set_model for the current model
     cudaStream_t stream = nullptr;       // the stream calls run on (own_stream unless bmpc_set_stream borrowed one)
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -67,7 +70,7 @@ struct bmpc_handle {
     uint32_t max_iter = 10000;
 
     // model
-    bool have_model = false, per_instance = false;
+    bool have_model = false, per_instance = false, specialize = true;
     long long model_count = 0;
     std::vector<double> hA, hB, hC, hQ, hR, hlo, hhi, hqdiag;   // shared model (host copies, already rounded to T)
     double hlambda = 0;

@@ -163,11 +163,11 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 8, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;
-    BMPC_CUDA(h->ops->info(h->precision, h->mode, h->per_instance, &ki));
+    BMPC_CUDA(h->solve_ops->info(h->precision, h->mode, h->per_instance, &ki));
     // persistent grid: one CTA per SM, never more CTAs than there are warps' worth of instances
     long long need_ctas = (count + ki.block - 1) / ki.block;
     int grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
-    BMPC_CUDA(h->ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
+    BMPC_CUDA(h->solve_ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev1, h->stream));
     h->timed = true;
     h->launches++;
@@ -225,7 +225,7 @@ int bmpc_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* reg
     if (!h) return fail(BMPC_E_INVALID, "bmpc_kernel_info: null handle");
     BMPC_CUDA(cudaSetDevice(h->device));
     KernelInfo ki;
-    BMPC_CUDA(h->ops->info(h->precision, h->mode, h->per_instance, &ki));
+    BMPC_CUDA(h->solve_ops->info(h->precision, h->mode, h->per_instance, &ki));
     if (grid) *grid = h->sm_count;
     if (block) *block = ki.block;
     if (smem_bytes) *smem_bytes = ki.smem_bytes;

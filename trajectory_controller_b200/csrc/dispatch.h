@@ -30,8 +30,11 @@ struct GenericCtor {
 
 struct KernelInfo { int block, smem_bytes, regs, warps, local_bytes; };
 
+// One (shape, structural pattern) instantiation family.  `ctor` is only provided by the dense pattern.
 struct ShapeOps {
     int S, I, N;
+    const char* pattern;                       // "dense", "bicycle4", ...
+    unsigned anz, aone, bnz, bone, cnz, qnz;   // solve_kernel.cuh Pattern bits
     cudaError_t (*solve)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
     cudaError_t (*ctor)(int precision, int mode, const GenericCtor& g, cudaStream_t st);
     cudaError_t (*info)(int precision, int mode, int pim, KernelInfo* out);

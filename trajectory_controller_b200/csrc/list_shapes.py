@@ -1,11 +1,13 @@
-"""Prints the template shapes of shapes.h as S_I_N tokens (used by the Makefile and build())."""
+"""Prints the (shape, pattern) instantiations of shapes.h as S_I_N_pattern tokens (used by the Makefile)."""
 import os
 import re
 
+
 def shapes():
     src = open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "shapes.h")).read()
-    line = [l for l in src.splitlines() if l.startswith("#define BMPC_SHAPES")][0]
-    return [tuple(int(x) for x in m) for m in re.findall(r"X\((\d+),\s*(\d+),\s*(\d+)\)", line)]
+    body = src[src.index("#define BMPC_SHAPES"):]
+    return [(int(a), int(b), int(c), d) for a, b, c, d in re.findall(r"X\((\d+),\s*(\d+),\s*(\d+),\s*(\w+)\)", body)]
+
 
 if __name__ == "__main__":
-    print(" ".join("%d_%d_%d" % s for s in shapes()))
+    print(" ".join("%d_%d_%d_%s" % s for s in shapes()))

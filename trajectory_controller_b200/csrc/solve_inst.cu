@@ -1,22 +1,30 @@
-// One translation unit per template shape: nvcc ... -DBMPC_S=4 -DBMPC_I=1 -DBMPC_N=30 solve_inst.cu
+// One translation unit per (template shape, structural pattern):
+//   nvcc ... -DBMPC_S=4 -DBMPC_I=1 -DBMPC_N=30 -DBMPC_PAT=bicycle4 solve_inst.cu
 // Instantiates the solve kernel for {fp64,fp32} x {exact,fast} x {shared,per-instance model} and the constructor
 // kernel (mpc.h:114-123), and exports them through a shape-erased ShapeOps table (dispatch.h).
 #include "ctor_kernel.cuh"
 #include "dispatch.h"
+#include "patterns.h"
 #include "solve_kernel.cuh"
 
 #ifndef BMPC_S
-#error "compile with -DBMPC_S= -DBMPC_I= -DBMPC_N="
+#error "compile with -DBMPC_S= -DBMPC_I= -DBMPC_N= -DBMPC_PAT="
+#endif
+#ifndef BMPC_PAT
+#define BMPC_PAT dense
 #endif
 
 namespace bmpc {
 namespace {
 constexpr int S_ = BMPC_S, I_ = BMPC_I, N_ = BMPC_N;
+using PAT_ = typename pat::BMPC_PAT<S_, I_>::type;
+constexpr bool kDense = (PAT_::ANZ == DensePattern<S_, I_>::ANZ && PAT_::AONE == 0u && PAT_::BNZ == DensePattern<S_, I_>::BNZ &&
+                         PAT_::BONE == 0u && PAT_::CNZ == DensePattern<S_, I_>::CNZ && PAT_::QNZ == DensePattern<S_, I_>::QNZ);
 
 template <typename T, bool EXACT, bool PIM>
 cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
 {
-    using L = Layout<T, S_, I_, N_, PIM>;
+    using L = Layout<T, S_, I_, N_, PIM, PAT_>;
     SolveParams<T, S_, I_, N_> p;
     for (int e = 0; e < S_ * S_; ++e) p.A[e] = PIM ? T(0) : (T)g.A[e];
     for (int e = 0; e < S_ * I_; ++e) p.B[e] = PIM ? T(0) : (T)g.B[e];
@@ -34,7 +42,7 @@ cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
     p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
     p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
     p.queue = g.queue;
-    auto kern = solve_kernel<T, S_, I_, N_, EXACT, PIM>;
+    auto kern = solve_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
@@ -44,9 +52,9 @@ cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
 template <typename T, bool EXACT, bool PIM>
 cudaError_t info_solve(KernelInfo* out)
 {
-    using L = Layout<T, S_, I_, N_, PIM>;
+    using L = Layout<T, S_, I_, N_, PIM, PAT_>;
     cudaFuncAttributes a;
-    cudaError_t e = cudaFuncGetAttributes(&a, solve_kernel<T, S_, I_, N_, EXACT, PIM>);
+    cudaError_t e = cudaFuncGetAttributes(&a, solve_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>);
     if (e != cudaSuccess) return e;
     out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
     out->local_bytes = (int)a.localSizeBytes;
@@ -80,16 +88,26 @@ cudaError_t solve_entry(int precision, int mode, int pim, const GenericSolve& g,
 { BMPC_DISPATCH(launch_solve, g, grid, st); }
 cudaError_t info_entry(int precision, int mode, int pim, KernelInfo* out)
 { BMPC_DISPATCH(info_solve, out); }
-cudaError_t ctor_entry(int precision, int mode, const GenericCtor& g, cudaStream_t st)
+template <bool DENSE>
+cudaError_t ctor_entry_t(int precision, int mode, const GenericCtor& g, cudaStream_t st)
 {
+    if constexpr (!DENSE) return cudaErrorNotSupported;   // the constructor recursion lives in the dense unit only
+    else {
     if (precision == 64) return mode == 0 ? launch_ctor<double, true>(g, st) : launch_ctor<double, false>(g, st);
     return mode == 0 ? launch_ctor<float, true>(g, st) : launch_ctor<float, false>(g, st);
+    }
 }
+cudaError_t ctor_entry(int precision, int mode, const GenericCtor& g, cudaStream_t st)
+{ return ctor_entry_t<kDense>(precision, mode, g, st); }
 }  // namespace
 
-#define BMPC_CAT_(a, b, c) bmpc_ops_##a##_##b##_##c
-#define BMPC_CAT(a, b, c) BMPC_CAT_(a, b, c)
-extern const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N);
-const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N) = {S_, I_, N_, solve_entry, ctor_entry, info_entry};
+#define BMPC_CAT_(a, b, c, d) bmpc_ops_##a##_##b##_##c##_##d
+#define BMPC_CAT(a, b, c, d) BMPC_CAT_(a, b, c, d)
+#define BMPC_STR_(x) #x
+#define BMPC_STR(x) BMPC_STR_(x)
+extern const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT);
+const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT) = {
+    S_, I_, N_, BMPC_STR(BMPC_PAT), PAT_::ANZ, PAT_::AONE, PAT_::BNZ, PAT_::BONE, PAT_::CNZ, PAT_::QNZ,
+    solve_entry, ctor_entry, info_entry};
 
 }  // namespace bmpc

@@ -9,7 +9,7 @@
 // Why this shape:
 //  * the gradient (mpc.h:275-283) is two length-N dependency chains of SxS mat-vecs; its rounding order forbids
 //    splitting one instance over lanes, but S rows x S products give each lane enough ILP to keep the FP64 pipe
-//    (16 lanes/SMSP/clk on B200) busy from ONE warp per SM sub-partition.  So occupancy is spent on storage, not
+//    (16 lanes/SMSP/clk on B200) busy from two warps per SM sub-partition.  So occupancy is spent on storage, not
 //    on latency hiding: u[] and the linear term MM[] live in registers (fully unrolled horizon), the stashed
 //    Q*M[] rows, the gradient and the Nesterov v[] in shared memory as [element][lane] (conflict-free 8-byte
 //    accesses, no HBM traffic inside the iteration loop).
@@ -18,6 +18,13 @@
 //    runs exactly one gradient-shaped pass for all 32 lanes.  The per-solve linear term (mpc.h:258-266) has the
 //    same recursion structure as the gradient, so SETUP lanes ride the same pass with predicated operands
 //    (MIXED pass); there is no divergent code of any size.
+//  * STRUCTURAL SPARSITY (Pattern): vehicle models are mostly zeros and ones (the (4,1) bicycle model has 7 non-zero
+//    entries in A, two of them exactly 1, and one in B; Q weights two of four states).  dlib multiplies them out
+//    densely.  A kernel instantiated for a pattern drops the terms whose coefficient is structurally zero and the
+//    multiplications by exactly 1 — both are exact in IEEE arithmetic (x + 0*y == x and 1*x == x for finite y; only
+//    the sign of a zero result can differ), so EXACT-mode parity is unaffected while the instruction count per
+//    horizon step falls ~3x and the fully unrolled pass fits the instruction cache.  The host picks, per model,
+//    the sparsest compiled pattern the model's entries satisfy (dispatch.h); the dense pattern always qualifies.
 #pragma once
 #include <stdint.h>
 
@@ -26,6 +33,14 @@
 namespace bmpc {
 
 constexpr int kSmemMax = 232448;  // 227 KB opt-in dynamic shared memory per CTA on sm_100
+
+// Bit e of *NZ: entry e (row-major) may be non-zero.  Bit e of *ONE: entry e is exactly 1.0 (implies NZ).
+template <unsigned ANZ_, unsigned AONE_, unsigned BNZ_, unsigned BONE_, unsigned CNZ_, unsigned QNZ_>
+struct Pattern {
+    static constexpr unsigned ANZ = ANZ_, AONE = AONE_, BNZ = BNZ_, BONE = BONE_, CNZ = CNZ_, QNZ = QNZ_;
+};
+template <int S, int I>
+using DensePattern = Pattern<(1u << (S * S)) - 1u, 0u, (1u << (S * I)) - 1u, 0u, (1u << S) - 1u, (1u << S) - 1u>;
 
 template <typename T, int S, int I, int N>
 struct SolveParams {
@@ -52,45 +67,56 @@ struct SolveParams {
     unsigned long long* queue;   // next unclaimed instance
 };
 
-constexpr int pow2_floor(int x) { return x >= 16 ? 16 : x >= 8 ? 8 : x >= 4 ? 4 : x >= 2 ? 2 : x >= 1 ? 1 : 0; }
+__host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n += int(x & 1u); x >>= 1; } return n; }
+__host__ __device__ constexpr int imax_c(int a, int b) { return a > b ? a : b; }
+__host__ __device__ constexpr int imin_c(int a, int b) { return a < b ? a : b; }
 
-template <typename T, int S, int I, int N, bool PIM>
+template <typename T, int S, int I, int N, bool PIM, typename PAT>
 struct Layout {
     static constexpr int NI = N * I;
-    // u[] in registers (fully unrolled horizon) when it costs at most 64 32-bit registers
-    static constexpr bool UREG = (NI * int(sizeof(T) / 4) <= 64);
-    static constexpr int O_QM = 0;                       // Q*M rows of horizon steps 0..N-2
-    static constexpr int O_DF = O_QM + (N - 1) * S;      // gradient
-    static constexpr int O_V = O_DF + NI;                // Nesterov v
+    static constexpr int WORDS = int(sizeof(T) / 4);
+    // u[] in registers (fully unrolled horizon) when it costs at most 64 32-bit registers; the linear term MM[] too
+    // when both together stay within 128
+    static constexpr bool UREG = (NI * WORDS <= 64);
+    static constexpr bool MMREG = UREG && (2 * NI * WORDS <= 128);
+    // Per horizon step: one slot per Q-weighted state row (the Q*M stash of the forward sweep, read back by the
+    // backward sweep) — and, once the backward sweep has consumed a step's stash, the same slots hold that step's
+    // gradient entries df[i][0..I).
+    static constexpr int SQ = popc_c(PAT::QNZ & ((1u << S) - 1u));
+    static constexpr int W = imax_c(SQ, I);
+    static constexpr int O_QM = 0;
+    static constexpr int O_V = O_QM + N * W;             // Nesterov v
     static constexpr int O_U = O_V + NI;
     static constexpr int O_MM = O_U + (UREG ? 0 : NI);   // linear term MM
-    static constexpr int O_MODEL = O_MM + NI;
+    static constexpr int O_MODEL = O_MM + (MMREG ? 0 : NI);
     static constexpr int M_A = 0, M_B = M_A + S * S, M_C = M_B + S * I, M_Q = M_C + S, M_R = M_Q + S,
                          M_LO = M_R + I, M_HI = M_LO + I, M_LEN = M_HI + I;
     static constexpr int ELEMS = O_MODEL + (PIM ? M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
-    static constexpr int WARPS = pow2_floor(FIT < (UREG ? 8 : 16) ? FIT : (UREG ? 8 : 16));
+    static constexpr int CAP = UREG ? 8 : 16;            // 255 registers/thread allow 8 warps per SM
+    static constexpr int WARPS = imin_c(FIT, CAP);
     static constexpr int THREADS = WARPS * 32;
     static constexpr int SMEM_BYTES = WARPS * WARP_BYTES;
     static_assert(WARPS >= 1, "horizon too long for the shared-memory resident layout");
+    // stash slot of state row r (rank of r among the Q-weighted rows)
+    __host__ __device__ static constexpr int qslot(int r) { return popc_c(PAT::QNZ & ((1u << r) - 1u)); }
 };
 
-#define BMPC_LOOP_N _Pragma("unroll")
-
-template <typename T, int S, int I, int N, bool EXACT, bool PIM>
+template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
 struct Solver {
-    using L = Layout<T, S, I, N, PIM>;
+    using L = Layout<T, S, I, N, PIM, PAT>;
     using P = SolveParams<T, S, I, N>;
     using A_ = Ar<T, EXACT>;
     static constexpr int NI = L::NI;
-    static constexpr bool UREG = L::UREG;
+    static constexpr bool UREG = L::UREG, MMREG = L::MMREG;
     static constexpr int UNROLL = UREG ? N : 2;        // horizon loops: full unroll keeps u[]/mm[] in registers
     static constexpr int UNROLL_K = UREG ? NI : 2;     // loops over the N*I control entries
 
     const P& p;
     T* sm;            // this lane's column of the warp's shared-memory block: element e at sm[e*32]
     T u[UREG ? NI : 1];
+    T mm[MMREG ? NI : 1];
 
     __device__ __forceinline__ Solver(const P& p_, T* sm_) : p(p_), sm(sm_) {}
 
@@ -105,43 +131,59 @@ struct Solver {
 
     __device__ __forceinline__ T getU(int k) const { if constexpr (UREG) return u[k]; else return sm[(L::O_U + k) * 32]; }
     __device__ __forceinline__ void setU(int k, T v) { if constexpr (UREG) u[k] = v; else sm[(L::O_U + k) * 32] = v; }
-    __device__ __forceinline__ T getMM(int k) const { return sm[(L::O_MM + k) * 32]; }
-    __device__ __forceinline__ void setMM(int k, T v) { sm[(L::O_MM + k) * 32] = v; }
+    __device__ __forceinline__ T getMM(int k) const { if constexpr (MMREG) return mm[k]; else return sm[(L::O_MM + k) * 32]; }
+    __device__ __forceinline__ void setMM(int k, T v) { if constexpr (MMREG) mm[k] = v; else sm[(L::O_MM + k) * 32] = v; }
 
     // The Q*M stash is written in the forward sweep and read back in the backward sweep of the SAME unrolled pass.
     // Through plain pointers nvcc forwards every stored value to its load, i.e. keeps N*S live values in registers
     // and spills them to local memory; volatile accesses make the round trip through shared memory real.
     __device__ __forceinline__ void stash_st(int off, T v) { *reinterpret_cast<volatile T*>(sm + off) = v; }
     __device__ __forceinline__ T stash_ld(int off) const { return *reinterpret_cast<const volatile T*>(sm + off); }
+    __device__ __forceinline__ T getDF(int k) const { return stash_ld((L::O_QM + (k / I) * L::W + (k % I)) * 32); }
 
-    // matrix.h:43-60 dot products, first term initialises
-    __device__ __forceinline__ T dotA(int r, const T* z) const
+    // One term of a matrix.h:43-60 dot product under the structural pattern: skipped when the coefficient is
+    // structurally zero, a plain copy/add when it is exactly one; the first surviving term initialises.
+    // (`nz`, `one`, `have` are compile-time constants after unrolling.)
+    __device__ __forceinline__ static void term(T& t, bool& have, bool nz, bool one, T coef, T z)
     {
-        T t = A_::mul(mA(r, 0), z[0]);
-#pragma unroll
-        for (int k = 1; k < S; ++k) t = A_::madd(t, mA(r, k), z[k]);
-        return t;
+        if (!nz) return;
+        if (one) t = have ? A_::add(t, z) : z;
+        else t = have ? A_::madd(t, coef, z) : A_::mul(coef, z);
+        have = true;
     }
-    __device__ __forceinline__ T dotAT(int r, const T* z) const   // trans(A)*z, matrix_utilities.h:375-410
+    __host__ __device__ static constexpr bool bit(unsigned m, int e) { return ((m >> e) & 1u) != 0u; }
+    __device__ __forceinline__ bool dotA(int r, const T* z, T& t) const        // A*z, row r
     {
-        T t = A_::mul(mA(0, r), z[0]);
+        bool have = false; t = T(0);
 #pragma unroll
-        for (int k = 1; k < S; ++k) t = A_::madd(t, mA(k, r), z[k]);
-        return t;
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::ANZ, r * S + k), bit(PAT::AONE, r * S + k), mA(r, k), z[k]);
+        return have;
     }
-    __device__ __forceinline__ T dotB(int r, const T* uu) const
+    __device__ __forceinline__ bool dotAT(int r, const T* z, T& t) const       // trans(A)*z, matrix_utilities.h:375-410
     {
-        T t = A_::mul(mB(r, 0), uu[0]);
+        bool have = false; t = T(0);
 #pragma unroll
-        for (int k = 1; k < I; ++k) t = A_::madd(t, mB(r, k), uu[k]);
-        return t;
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::ANZ, k * S + r), bit(PAT::AONE, k * S + r), mA(k, r), z[k]);
+        return have;
     }
-    __device__ __forceinline__ T dotBT(int j, const T* z) const
+    __device__ __forceinline__ bool dotB(int r, const T* uu, T& t) const       // B*u, row r
     {
-        T t = A_::mul(mB(0, j), z[0]);
+        bool have = false; t = T(0);
 #pragma unroll
-        for (int k = 1; k < S; ++k) t = A_::madd(t, mB(k, j), z[k]);
-        return t;
+        for (int k = 0; k < I; ++k) term(t, have, bit(PAT::BNZ, r * I + k), bit(PAT::BONE, r * I + k), mB(r, k), uu[k]);
+        return have;
+    }
+    __device__ __forceinline__ bool dotBT(int j, const T* z, T& t) const       // trans(B)*z, row j
+    {
+        bool have = false; t = T(0);
+#pragma unroll
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::BNZ, k * I + j), bit(PAT::BONE, k * I + j), mB(k, j), z[k]);
+        return have;
+    }
+    // a + b where either side may be structurally absent (x + 0 == x exactly)
+    __device__ __forceinline__ static T add_opt(bool ha, T a, bool hb, T b)
+    {
+        return ha ? (hb ? A_::add(a, b) : a) : (hb ? b : T(0));
     }
 
     // One gradient-shaped pass.
@@ -163,11 +205,12 @@ struct Solver {
             for (int j = 0; j < I; ++j) u0v[j] = getU(j);
 #pragma unroll
             for (int r = 0; r < S; ++r) {
-                T tb = dotB(r, u0v);                                   // M[0] = B*controls[0]          mpc.h:275
+                T tb; const bool hb = dotB(r, u0v, tb);               // M[0] = B*controls[0]          mpc.h:275
                 if constexpr (MIXED) {
-                    T ta = A_::add(dotA(r, xs), mC(r));               // M[0] = A*initial_state + C   mpc.h:258
-                    m[r] = setup ? ta : tb;
-                } else m[r] = tb;
+                    T ta; const bool ha = dotA(r, xs, ta);            // M[0] = A*initial_state + C   mpc.h:258
+                    const T tas = add_opt(ha, ta, bit(PAT::CNZ, r), mC(r));
+                    m[r] = setup ? tas : (hb ? tb : T(0));
+                } else m[r] = hb ? tb : T(0);
             }
         }
         T w[S];
@@ -180,27 +223,32 @@ struct Solver {
                 for (int j = 0; j < I; ++j) ui[j] = getU(i * I + j);
 #pragma unroll
                 for (int r = 0; r < S; ++r) {
-                    T t1 = dotA(r, m);                                  // A*M[i-1]
-                    T ad = dotB(r, ui);                                 // + B*controls[i]               mpc.h:277
-                    if constexpr (MIXED) ad = setup ? mC(r) : ad;      // + C                           mpc.h:260
-                    mn[r] = A_::add(t1, ad);
+                    T t1; const bool h1 = dotA(r, m, t1);              // A*M[i-1]
+                    T ad; bool hb = dotB(r, ui, ad);                   // + B*controls[i]               mpc.h:277
+                    if constexpr (MIXED) {                             // + C                           mpc.h:260
+                        const bool hc = bit(PAT::CNZ, r);
+                        if (hb || hc) { ad = setup ? (hc ? mC(r) : T(0)) : (hb ? ad : T(0)); hb = true; }
+                    }
+                    mn[r] = add_opt(h1, t1, hb, ad);
                 }
 #pragma unroll
                 for (int r = 0; r < S; ++r) m[r] = mn[r];
             }
 #pragma unroll
             for (int r = 0; r < S; ++r) {
-                T d = m[r];
-                if constexpr (MIXED) {                                  // M[i] - target[i]              mpc.h:262
-                    T tg = tgc[r];
-                    if (p.target_full && setup) {
-                        int ph = p.head + i; if (ph >= N) ph -= N;
-                        tg = p.target[((long long)ph * S + r) * p.stride + inst];
+                if (bit(PAT::QNZ, r)) {
+                    T d = m[r];
+                    if constexpr (MIXED) {                              // M[i] - target[i]              mpc.h:262
+                        T tg = tgc[r];
+                        if (p.target_full && setup) {
+                            int ph = p.head + i; if (ph >= N) ph -= N;
+                            tg = p.target[((long long)ph * S + r) * p.stride + inst];
+                        }
+                        d = setup ? A_::sub(m[r], tg) : d;
                     }
-                    d = setup ? A_::sub(m[r], tg) : d;
-                }
-                T q = A_::mul(mQ(r), d);                                // diagm(Q)*M[i]                 mpc.h:262,279
-                if (i < N - 1) stash_st((L::O_QM + i * S + r) * 32, q); else w[r] = q;
+                    T q = A_::mul(mQ(r), d);                            // diagm(Q)*M[i]                 mpc.h:262,279
+                    if (i < N - 1) stash_st((L::O_QM + i * L::W + L::qslot(r)) * 32, q); else w[r] = q;
+                } else if (i == N - 1) w[r] = T(0);                     // Q(r) == 0: the scaled row is a zero
             }
         }
         // ---- backward recursion, gradient, arg-max ---------------------------------------------------------------
@@ -210,12 +258,12 @@ struct Solver {
 #pragma unroll
             for (int j = I - 1; j >= 0; --j) {
                 const int k = i * I + j;
-                T bt = dotBT(j, w);                                     // trans(B)*M[i]                 mpc.h:266,283
+                T bt; const bool hbt = dotBT(j, w, bt);                 // trans(B)*M[i]                 mpc.h:266,283
                 T uij = getU(k);
                 T mmv = getMM(k);
-                if constexpr (MIXED) { mmv = setup ? bt : mmv; setMM(k, mmv); }
-                T dfv = A_::add(A_::add(mmv, bt), A_::mul(mR(j), uij)); // MM + B'M + diagm(R)*u         mpc.h:283
-                sm[(L::O_DF + k) * 32] = dfv;
+                if constexpr (MIXED) { mmv = setup ? (hbt ? bt : T(0)) : mmv; setMM(k, mmv); }
+                T dfv = A_::add(add_opt(true, mmv, hbt, bt), A_::mul(mR(j), uij)); // MM + B'M + diagm(R)*u  mpc.h:283
+                stash_st((L::O_QM + i * L::W + j) * 32, dfv);           // this step's stash slots are dead by now
                 const bool active = (uij <= mLo(j) && dfv > T(0)) || (uij >= mHi(j) && dfv < T(0));   // mpc.h:296-299
                 const T a = absval(dfv);
                 if (!active && a >= max_df && a > T(0)) { max_df = a; max_idx = k; max_val = dfv; }  // mpc.h:301-306
@@ -223,8 +271,13 @@ struct Solver {
             if (i > 0) {
                 T wn[S];
 #pragma unroll
-                for (int r = 0; r < S; ++r)                              // M[i-1] += trans(A)*M[i]       mpc.h:264,281
-                    wn[r] = A_::add(stash_ld((L::O_QM + (i - 1) * S + r) * 32), dotAT(r, w));
+                for (int r = 0; r < S; ++r) {                            // M[i-1] += trans(A)*M[i]       mpc.h:264,281
+                    T t; const bool h = dotAT(r, w, t);
+                    const bool hq = bit(PAT::QNZ, r);
+                    T st = T(0);
+                    if (hq) st = stash_ld((L::O_QM + (i - 1) * L::W + L::qslot(r)) * 32);
+                    wn[r] = add_opt(hq, st, h, t);
+                }
 #pragma unroll
                 for (int r = 0; r < S; ++r) w[r] = wn[r];
             }
@@ -233,13 +286,13 @@ struct Solver {
 };
 
 // The kernel.  grid = #SMs (persistent), block = WARPS*32, dynamic smem = Layout::SMEM_BYTES.
-template <typename T, int S, int I, int N, bool EXACT, bool PIM>
-__global__ void __launch_bounds__(Layout<T, S, I, N, PIM>::THREADS, 1)
+template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
+__global__ void __launch_bounds__((Layout<T, S, I, N, PIM, PAT>::THREADS), 1)
 solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
 {
-    using L = Layout<T, S, I, N, PIM>;
+    using L = Layout<T, S, I, N, PIM, PAT>;
     using A_ = Ar<T, EXACT>;
-    using SV = Solver<T, S, I, N, EXACT, PIM>;
+    using SV = Solver<T, S, I, N, EXACT, PIM, PAT>;
     constexpr int NI = L::NI;
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -364,7 +417,7 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                         const int j = k % I;
                         const T lo = sv.mLo(j), hi = sv.mHi(j);
                         const T v_old = sm[(L::O_V + k) * 32];
-                        const T vn = clamp_m(A_::sub(sv.getU(k), A_::mul(inv_lambda, sm[(L::O_DF + k) * 32])), lo, hi);
+                        const T vn = clamp_m(A_::sub(sv.getU(k), A_::mul(inv_lambda, sv.getDF(k))), lo, hi);
                         sm[(L::O_V + k) * 32] = vn;
                         sv.setU(k, clamp_m(A_::madd(vn, beta, A_::sub(vn, v_old)), lo, hi));
                     }

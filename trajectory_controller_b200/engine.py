@@ -38,6 +38,8 @@ SIGNATURES = {
     "bmpc_last_error": (C.c_char_p, []),
     "bmpc_version": (C.c_char_p, []),
     "bmpc_set_model": (C.c_int, [C.c_void_p] + [_dp] * 7 + [C.c_int, C.c_int64]),
+    "bmpc_set_specialization": (C.c_int, [C.c_void_p, C.c_int]),
+    "bmpc_pattern_name": (C.c_char_p, [C.c_void_p]),
     "bmpc_set_options": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64]),
     "bmpc_get_options": (C.c_int, [C.c_void_p, _dp, C.POINTER(C.c_uint64)]),
     "bmpc_get_derived": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp]),
@@ -129,6 +131,14 @@ class BatchedMPC:
         count = arrs[0].shape[0] if per_instance else 1
         _check(lib().bmpc_set_model(self._h, *[_p(a) for a in arrs], int(per_instance), count))
         return self
+
+    def set_specialization(self, enable: bool):
+        """False: always run the dense kernel (effective at the next set_model)."""
+        _check(lib().bmpc_set_specialization(self._h, int(enable)))
+        return self
+
+    def pattern_name(self) -> str:
+        return lib().bmpc_pattern_name(self._h).decode()
 
     def set_epsilon(self, eps: float):
         _check(lib().bmpc_set_options(self._h, eps, self.get_max_iterations()))
