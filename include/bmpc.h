@@ -98,6 +98,10 @@ int bmpc_reset(bmpc_t* h);
 int bmpc_get_controls(bmpc_t* h, int64_t first, int64_t count, double* controls);
 /* EXTENSION (dlib::mpc has no such setter): seed the warm start. */
 int bmpc_set_controls(bmpc_t* h, int64_t first, int64_t count, const double* controls);
+/* Copy-construction / assignment of controller objects (dlib::mpc is a by-value type, mpc.h:349-362): controls,
+ * targets, the stale-v storage and the options of `src` into `dst` (device-to-device).  Both handles must have the
+ * same shape, precision and capacity and live on the same device.  The model is not copied (call bmpc_set_model). */
+int bmpc_copy_state(bmpc_t* dst, bmpc_t* src);
 
 /* ---- solve  (mpc.h:216-240 operator(), :253-347 solve_linear_mpc) --------------------------------------------- */
 /* Host buffers: x0[count][S] in; u0[count][I], iters[count] (may be NULL), status[count] (may be NULL) out.

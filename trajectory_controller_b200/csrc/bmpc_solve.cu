@@ -126,6 +126,30 @@ int bmpc_set_controls(bmpc_t* h, int64_t first, int64_t count, const double* con
     return BMPC_OK;
 }
 
+int bmpc_copy_state(bmpc_t* dst, bmpc_t* src)
+{
+    if (!dst || !src) return fail(BMPC_E_INVALID, "bmpc_copy_state: null handle");
+    if (dst == src) return BMPC_OK;
+    if (dst->S != src->S || dst->I != src->I || dst->N != src->N || dst->precision != src->precision ||
+        dst->cap != src->cap || dst->device != src->device)
+        return fail(BMPC_E_INVALID, "bmpc_copy_state: handles differ in shape, precision, capacity or device");
+    BMPC_CUDA(cudaSetDevice(dst->device));
+    BMPC_CUDA(cudaStreamSynchronize(src->stream));
+    BMPC_CUDA(cudaMemcpyAsync(dst->controls.p, src->controls.p, src->controls.bytes, cudaMemcpyDeviceToDevice, dst->stream));
+    BMPC_CUDA(cudaMemcpyAsync(dst->vstate.p, src->vstate.p, src->vstate.bytes, cudaMemcpyDeviceToDevice, dst->stream));
+    BMPC_CUDA(cudaMemcpyAsync(dst->target_const.p, src->target_const.p, src->target_const.bytes, cudaMemcpyDeviceToDevice, dst->stream));
+    if (src->full_targets) {
+        BMPC_CUDA(dst->target_full.reserve(src->target_full.bytes));
+        BMPC_CUDA(cudaMemcpyAsync(dst->target_full.p, src->target_full.p, src->target_full.bytes, cudaMemcpyDeviceToDevice, dst->stream));
+    }
+    dst->full_targets = src->full_targets;
+    dst->head = src->head;
+    dst->eps = src->eps;
+    dst->max_iter = src->max_iter;
+    BMPC_CUDA(cudaStreamSynchronize(dst->stream));
+    return BMPC_OK;
+}
+
 int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
 {
     if (!h || !x0) return fail(BMPC_E_INVALID, "bmpc_upload_x0: null argument");

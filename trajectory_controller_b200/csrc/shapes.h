@@ -9,8 +9,12 @@
 // Patterns (patterns.h): `dense` accepts every model of the shape and also carries the constructor kernel;
 // the named ones drop structurally-zero / exactly-one coefficients for the models this project ships with.
 #pragma once
+#ifdef BMPC_QUICK   /* developer A/B builds: only the benchmark shape (make QUICK=1 OUT=...) */
+#define BMPC_SHAPES(X) X(4, 1, 30, dense) X(4, 1, 30, bicycle4)
+#else
 #define BMPC_SHAPES(X)                                                                                        \
     X(2, 2, 4, dense) X(2, 1, 30, dense) X(4, 1, 10, dense) X(4, 1, 30, dense) X(4, 1, 60, dense)            \
     X(4, 1, 100, dense) X(4, 2, 10, dense) X(3, 2, 7, dense)                                                  \
     X(2, 2, 4, tobi) X(2, 1, 30, kat) X(4, 1, 10, bicycle4) X(4, 1, 30, bicycle4) X(4, 1, 60, bicycle4)      \
     X(4, 1, 100, bicycle4)
+#endif

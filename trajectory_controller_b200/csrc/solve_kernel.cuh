@@ -94,7 +94,10 @@ struct Layout {
     static constexpr int ELEMS = O_MODEL + (PIM ? M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
-    static constexpr int CAP = UREG ? 8 : 16;            // 255 registers/thread allow 8 warps per SM
+#ifndef BMPC_CAP_WARPS
+#define BMPC_CAP_WARPS 8
+#endif
+    static constexpr int CAP = UREG ? BMPC_CAP_WARPS : 16;   // 255 registers/thread allow 8 warps per SM
     static constexpr int WARPS = imin_c(FIT, CAP);
     static constexpr int THREADS = WARPS * 32;
     static constexpr int SMEM_BYTES = WARPS * WARP_BYTES;
@@ -253,6 +256,9 @@ struct Solver {
         }
         // ---- backward recursion, gradient, arg-max ---------------------------------------------------------------
         max_df = T(0); max_idx = 0; max_val = T(0);
+        T lo_[I], hi_[I];
+#pragma unroll
+        for (int j = 0; j < I; ++j) { lo_[j] = mLo(j); hi_[j] = mHi(j); }
 #pragma unroll(UNROLL)
         for (int i = N - 1; i >= 0; --i) {
 #pragma unroll
@@ -264,7 +270,8 @@ struct Solver {
                 if constexpr (MIXED) { mmv = setup ? (hbt ? bt : T(0)) : mmv; setMM(k, mmv); }
                 T dfv = A_::add(add_opt(true, mmv, hbt, bt), A_::mul(mR(j), uij)); // MM + B'M + diagm(R)*u  mpc.h:283
                 stash_st((L::O_QM + i * L::W + j) * 32, dfv);           // this step's stash slots are dead by now
-                const bool active = (uij <= mLo(j) && dfv > T(0)) || (uij >= mHi(j) && dfv < T(0));   // mpc.h:296-299
+                // all four comparisons evaluated (no short-circuit: a lazily fetched bound serialises the sweep)
+                const bool active = ((uij <= lo_[j]) & (dfv > T(0))) | ((uij >= hi_[j]) & (dfv < T(0)));   // mpc.h:296-299
                 const T a = absval(dfv);
                 if (!active && a >= max_df && a > T(0)) { max_df = a; max_idx = k; max_val = dfv; }  // mpc.h:301-306
             }

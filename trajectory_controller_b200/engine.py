@@ -16,7 +16,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbmpc.so")
+# BMPC_LIB: developer override to A/B-test another build of the same ABI (never a fallback: the file must exist)
+LIB_PATH = os.environ.get("BMPC_LIB") or os.path.join(_HERE, "libbmpc.so")
 
 FP64, FP32 = 64, 32
 EXACT, FAST = 0, 1
@@ -48,6 +49,7 @@ SIGNATURES = {
     "bmpc_reset": (C.c_int, [C.c_void_p]),
     "bmpc_get_controls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, _dp]),
     "bmpc_set_controls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, _dp]),
+    "bmpc_copy_state": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bmpc_solve": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _u32p, _u8p, C.c_uint]),
     "bmpc_upload_x0": (C.c_int, [C.c_void_p, C.c_int64, _dp]),
     "bmpc_solve_resident_async": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint]),
