@@ -46,3 +46,40 @@ def test_cpp_boundary_on_gpu(built, exe):
     r = subprocess.run([os.path.join(built, exe)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "0 failed" in r.stdout
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Cycle-by-cycle comparison of three builds of the MODULE library over one scenario (tests/cpp/module_driver.cpp).
+# Golden = the reference's OWN module source + the real dlib::mpc (oracle/_ref/libref_module_dlib.so, CPU), recorded
+# in tests/golden/module_cycles.txt by:  tests/cpp/build/module_driver oracle/_ref/libref_module_dlib.so
+GOLDEN_CYCLES = os.path.join(ROOT, "tests", "golden", "module_cycles.txt")
+REF_MODULE_DLIB = os.path.join(ROOT, "oracle", "_ref", "libref_module_dlib.so")
+REF_MODULE_BMPC = os.path.join(BUILD, "libref_module_bmpc.so")
+OUR_MODULE = os.path.join(CPP, "build", "libtrajectory_point_controller.so")
+
+
+def _drive(built, module_path):
+    r = subprocess.run([os.path.join(built, "module_driver"), module_path], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return r.stdout.splitlines()
+
+
+def test_golden_cycles_come_from_the_reference_module(built):
+    """Pins the golden file: the unmodified reference module + real dlib reproduces it (needs /root/reference)."""
+    if not os.path.exists(REF_MODULE_DLIB):
+        pytest.skip("oracle/_ref/libref_module_dlib.so not built (no /root/reference on this machine)")
+    assert _drive(built, REF_MODULE_DLIB) == open(GOLDEN_CYCLES).read().splitlines()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["rehosted_module", "reference_source_on_facade"])
+def test_module_cycles_match_reference(built, which):
+    """CAR / TRAJECTORY_POINT outputs of 48 cycles (tobiMPC incl. FOH look-ahead, crossing slow-down, lane-change
+    indicators, IDLE, PID fallback) are identical — every float bit — to the reference module on the CPU."""
+    path = OUR_MODULE if which == "rehosted_module" else REF_MODULE_BMPC
+    if not os.path.exists(path):
+        pytest.skip(f"{path} was not prebuilt (needs /root/reference at build time)")
+    got, want = _drive(built, path), open(GOLDEN_CYCLES).read().splitlines()
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g == w

@@ -20,3 +20,11 @@ Blackboard& Blackboard::instance()
     return b;
 }
 }  // namespace lms
+
+// Stub of the missing andromeda solver (shim/andromeda.h): no motion.
+extern "C" void call_andromeda(double*, double*, double*, double*, double*, double*, double, double*, double*, double,
+                               double, double, double, double, double, double, double, double, double* v_star,
+                               double* u_1_star, double* u_2_star)
+{
+    for (int i = 0; i < 10; ++i) { v_star[i] = 0; u_1_star[i] = 0; u_2_star[i] = 0; }
+}
