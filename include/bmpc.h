@@ -140,6 +140,47 @@ int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints,
                         int64_t stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* out_px,
                         float* out_py, float* out_dx, float* out_dy, float* out_vel);
 
+/* ---- closed loop on the device  (BASELINE.json configs[4]) ------------------------------------
+ * Every tick, for every vehicle, without a host round trip:
+ *   sample the world path into a vehicle-frame polyline of P float points (what the TRAJECTORY channel carries)
+ *   -> getTrajectoryPoint(lookahead)                       src/trajectory_point_follower.cpp:392-443
+ *   -> target = (point.y, atan(dir.y/dir.x), 0, 0) for every horizon step      src/...:84-85, :368-371
+ *   -> persistent-controller solve from x0 = (0, 0, delta, delta_dot)          mpc.h:216-240 (BMPC_WARM)
+ *   -> plant step with u0.
+ * The reference has no plant and no path sampler: those two are HARNESS code, defined here so that the CPU restatement
+ * (oracle/closed_loop_oracle.c) and the kernels compute the same numbers bit for bit — only + - * / sqrt, each
+ * rounded on its own, in this order:
+ *   k0      = first index with path_x[k] > X, clamped to [0, npath - P]
+ *   point i = world point k0 + i: (dx, dy) = (path_x - X, path_y - Y) in double;
+ *             position = ((float)(c*dx + s*dy), (float)(c*dy - s*dx)); the direction of the selected point is the
+ *             world tangent rotated the same way; velocity = (float)v
+ *   phi     = bmpc_harness_atan(dir.y / dir.x) in double if dir.x > 0, else +-pi/2 by the sign of dir.y
+ *   plant   : delta' = (A22*delta + A23*ddelta) + B2*u;  ddelta' = (A32*delta + A33*ddelta) + B3*u;
+ *             dpsi = ((T*v)/l)*delta;  (c', s') = (c - s*dpsi, s + c*dpsi) / sqrt(c'^2 + s'^2);
+ *             X' = X + (T*v)*c;  Y' = Y + (T*v)*s          (old c, s, delta on the right-hand sides)
+ *   bmpc_harness_atan(t): t1 = t/(1+sqrt(1+t*t)); t2 = t1/(1+sqrt(1+t1*t1)); z = t2*t2;
+ *             4 * t2 * (1 - z/3 + z^2/5 - ... - z^11/23) by Horner from the last term.
+ * Requires a shared (not per-instance) model with S = 4, I = 1 (the survey's bicycle model). */
+typedef struct bmpc_cl_config {
+    double v;            /* speed [m/s] */
+    double T;            /* plant step [s] (src/trajectory_point_follower.cpp:96) */
+    double l;            /* wheelbase [m] (include/trajectory_point_follower.h:47) */
+    double lookahead;    /* d = regelpunktMin + v*regelpunktSlope (src/...:71), evaluated by the caller; used as float */
+    int32_t P;           /* polyline points per tick */
+    int32_t npath;       /* world path points */
+} bmpc_cl_config;
+/* path_*: npath doubles each (world positions, ascending x, and unit tangents); pose0[count][4] = X, Y, cos psi, sin psi;
+ * act0[count][2] = delta, delta_dot (NULL = zeros).  Resets the controllers (fresh dlib::mpc objects). */
+int bmpc_cl_init(bmpc_t* h, int64_t count, const bmpc_cl_config* cfg, const double* path_x, const double* path_y,
+                 const double* path_tx, const double* path_ty, const double* pose0, const double* act0);
+/* `ticks` control ticks for all vehicles; kernels only, synchronous on return. */
+int bmpc_cl_run(bmpc_t* h, int ticks);
+/* State after the last tick; any pointer may be NULL.  pose[count][4], act[count][2], u0[count] (last command),
+ * target[count][2] (last y_soll, phi_soll), idx[count] (last selected polyline index), iters_total[count] (solver
+ * iterations summed over all ticks), iters_max[count]. */
+int bmpc_cl_get(bmpc_t* h, int64_t count, double* pose, double* act, double* u0, double* target, int32_t* idx,
+                uint64_t* iters_total, uint32_t* iters_max);
+
 #ifdef __cplusplus
 }
 #endif

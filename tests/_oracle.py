@@ -92,6 +92,27 @@ class Oracle:
     def controller(self, model, N):
         return OracleController(self, model, N)
 
+    # ---- closed loop (oracle/closed_loop_oracle.c) ------------------------------------------------------------------
+    def closed_loop(self, model, N, path, pose0, ticks, act0=None, v=1.0, T=0.1, l=0.21, lookahead=None, P=64,
+                    eps=0.01, max_iter=10000, nthreads=8):
+        ma = _ModelArgs(model)
+        px, py, tx, ty = (_c64(a) for a in path)
+        pose = _c64(pose0).copy(); n = pose.shape[0]
+        act = np.zeros((n, 2)) if act0 is None else _c64(act0).copy()
+        u0 = np.zeros(n); tgt = np.zeros((n, 2)); idx = np.zeros(n, dtype=np.int32)
+        itot = np.zeros(n, dtype=np.uint64); imax = np.zeros(n, dtype=np.uint32)
+        f = self.lib.orc_closed_loop
+        f.restype = C.c_int
+        f.argtypes = [C.c_long, C.c_int] + [_dp] * 7 + [C.c_double, C.c_ulong] + [C.c_double] * 4 + [C.c_int, C.c_int] + \
+            [_dp] * 4 + [C.c_int] + [_dp] * 4 + [C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.c_int]
+        rc = f(n, N, *ma.ptrs, eps, max_iter, v, T, l, (0.6 + 0.1 * v) if lookahead is None else lookahead, P,
+               px.shape[0], _d(px), _d(py), _d(tx), _d(ty), ticks, _d(pose), _d(act), _d(u0), _d(tgt),
+               idx.ctypes.data_as(C.POINTER(C.c_int32)), itot.ctypes.data_as(C.POINTER(C.c_uint64)),
+               imax.ctypes.data_as(C.POINTER(C.c_uint32)), nthreads)
+        if rc != 0:
+            raise ValueError("oracle: bad closed-loop arguments")
+        return dict(pose=pose, act=act, u0=u0, target=tgt, idx=idx, iters_total=itot, iters_max=imax)
+
     # ---- point extraction ---------------------------------------------------------------------------------
     def extract(self, px, py, dx, dy, vel, dist, npoints=None, layout="shared"):
         """layout 'shared': component arrays [P]; 'pb': [P][B] (point-major); 'bp': [B][P]."""

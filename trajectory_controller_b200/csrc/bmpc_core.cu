@@ -163,7 +163,7 @@ void bmpc_destroy(bmpc_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
                       &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
-                      &h->stage, &h->small};
+                      &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : h->ex) b.release();
     if (h->pinned) cudaFreeHost(h->pinned);

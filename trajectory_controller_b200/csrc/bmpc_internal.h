@@ -87,4 +87,15 @@ struct bmpc_handle {
     void* pinned = nullptr;       // host pinned mirror for small transfers
     size_t pinned_bytes = 0;
     bmpc::DevBuf ex[16];          // trajectory-point extraction buffers
+
+    // closed loop (closed_loop.cu)
+    bool cl_ready = false;
+    long long cl_count = 0;
+    bmpc_cl_config cl_cfg{};
+    bmpc::DevBuf cl_path;         // 4 x npath doubles: x, y, tx, ty
+    bmpc::DevBuf cl_pose;         // [4][cap] doubles: X, Y, c, s
+    bmpc::DevBuf cl_tgt;          // [2][cap] doubles: last y_soll, phi_soll
+    bmpc::DevBuf cl_idx;          // int32 [cap]
+    bmpc::DevBuf cl_itot;         // uint64 [cap]
+    bmpc::DevBuf cl_imax;         // uint32 [cap]
 };

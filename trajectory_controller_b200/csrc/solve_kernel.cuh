@@ -106,6 +106,20 @@ struct Layout {
     __host__ __device__ static constexpr int qslot(int r) { return popc_c(PAT::QNZ & ((1u << r) - 1u)); }
 };
 
+template <typename T> struct BitsOf;
+template <> struct BitsOf<double> {
+    using type = unsigned long long;
+    static constexpr type abs_mask = 0x7fffffffffffffffull, inf = 0x7ff0000000000000ull;
+    __device__ __forceinline__ static type to(double x) { return (type)__double_as_longlong(x); }
+    __device__ __forceinline__ static double from(type b) { return __longlong_as_double((long long)b); }
+};
+template <> struct BitsOf<float> {
+    using type = unsigned;
+    static constexpr type abs_mask = 0x7fffffffu, inf = 0x7f800000u;
+    __device__ __forceinline__ static type to(float x) { return __float_as_uint(x); }
+    __device__ __forceinline__ static float from(type b) { return __uint_as_float(b); }
+};
+
 template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
 struct Solver {
     using L = Layout<T, S, I, N, PIM, PAT>;
@@ -115,6 +129,11 @@ struct Solver {
     static constexpr bool UREG = L::UREG, MMREG = L::MMREG;
     static constexpr int UNROLL = UREG ? N : 2;        // horizon loops: full unroll keeps u[]/mm[] in registers
     static constexpr int UNROLL_K = UREG ? NI : 2;     // loops over the N*I control entries
+
+    using Bits = typename BitsOf<T>::type;
+    static constexpr Bits kAbsMask = BitsOf<T>::abs_mask, kInfBits = BitsOf<T>::inf;
+    __device__ __forceinline__ static Bits to_bits(T x) { return BitsOf<T>::to(x); }
+    __device__ __forceinline__ static T from_bits(Bits b) { return BitsOf<T>::from(b); }
 
     const P& p;
     T* sm;            // this lane's column of the warp's shared-memory block: element e at sm[e*32]
@@ -256,6 +275,7 @@ struct Solver {
         }
         // ---- backward recursion, gradient, arg-max ---------------------------------------------------------------
         max_df = T(0); max_idx = 0; max_val = T(0);
+        Bits max_key = 0; bool max_neg = false;
         T lo_[I], hi_[I];
 #pragma unroll
         for (int j = 0; j < I; ++j) { lo_[j] = mLo(j); hi_[j] = mHi(j); }
@@ -271,9 +291,15 @@ struct Solver {
                 T dfv = A_::add(add_opt(true, mmv, hbt, bt), A_::mul(mR(j), uij)); // MM + B'M + diagm(R)*u  mpc.h:283
                 stash_st((L::O_QM + i * L::W + j) * 32, dfv);           // this step's stash slots are dead by now
                 // all four comparisons evaluated (no short-circuit: a lazily fetched bound serialises the sweep)
-                const bool active = ((uij <= lo_[j]) & (dfv > T(0))) | ((uij >= hi_[j]) & (dfv < T(0)));   // mpc.h:296-299
-                const T a = absval(dfv);
-                if (!active && a >= max_df && a > T(0)) { max_df = a; max_idx = k; max_val = dfv; }  // mpc.h:301-306
+                // The bound tests stay floating-point compares; sign, magnitude and the running maximum are done on
+                // the bit patterns (integer pipe): for |df| in (0, +inf] the IEEE order equals the unsigned order of
+                // the bits, zeros and NaNs are never selected (as in mpc.h:301: abs(NaN) > max_df is false).
+                const Bits bits = to_bits(dfv);
+                const Bits a = bits & kAbsMask;
+                const bool neg = (bits & ~kAbsMask) != 0;
+                const bool sel = (Bits)(a - 1) < kInfBits;                       // 0 < |df| <= inf, not NaN
+                const bool active = neg ? (uij >= hi_[j]) : (uij <= lo_[j]);     // mpc.h:296-299 given df != 0
+                if (sel & !active & (a >= max_key)) { max_key = a; max_idx = k; max_neg = neg; }   // mpc.h:301-306
             }
             if (i > 0) {
                 T wn[S];
@@ -289,6 +315,8 @@ struct Solver {
                 for (int r = 0; r < S; ++r) w[r] = wn[r];
             }
         }
+        max_df = from_bits(max_key);
+        max_val = from_bits(max_key | (max_neg ? ~kAbsMask : Bits(0)));
     }
 };
 

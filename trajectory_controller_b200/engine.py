@@ -61,7 +61,17 @@ SIGNATURES = {
     "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
     "bmpc_probe_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "bmpc_extract_points": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
+    "bmpc_cl_init": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p] + [_dp] * 6),
+    "bmpc_cl_run": (C.c_int, [C.c_void_p, C.c_int]),
+    "bmpc_cl_get": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _dp, _dp, _i32p, C.POINTER(C.c_uint64), _u32p]),
 }
+
+
+class ClConfig(C.Structure):
+    """bmpc_cl_config (include/bmpc.h)."""
+    _fields_ = [("v", C.c_double), ("T", C.c_double), ("l", C.c_double), ("lookahead", C.c_double),
+                ("P", C.c_int32), ("npath", C.c_int32)]
+
 
 _lib = None
 
@@ -252,6 +262,27 @@ class BatchedMPC:
         t, g = C.c_double(), C.c_double()
         _check(lib().bmpc_probe_peak(self._h, precision, int(fused), C.byref(t), C.byref(g)))
         return t.value, g.value
+
+    # ---- closed loop on the device ------------------------------------------------------------------------------------------
+    def cl_init(self, path, pose0, act0=None, v=1.0, T=0.1, l=0.21, lookahead=None, P=64):
+        """path: (x, y, tx, ty) world polyline arrays; pose0 [count][4] = X, Y, cos psi, sin psi."""
+        px, py, tx, ty = (_c64(a) for a in path)
+        pose0 = _c64(pose0)
+        cfg = ClConfig(v, T, l, (0.6 + 0.1 * v) if lookahead is None else lookahead, P, px.shape[0])
+        a0 = None if act0 is None else _c64(act0)
+        _check(lib().bmpc_cl_init(self._h, pose0.shape[0], C.byref(cfg), _p(px), _p(py), _p(tx), _p(ty), _p(pose0), _p(a0)))
+        self._cl_count = pose0.shape[0]
+
+    def cl_run(self, ticks: int):
+        _check(lib().bmpc_cl_run(self._h, ticks))
+
+    def cl_get(self):
+        n = self._cl_count
+        out = dict(pose=np.empty((n, 4)), act=np.empty((n, 2)), u0=np.empty(n), target=np.empty((n, 2)),
+                   idx=np.empty(n, dtype=np.int32), iters_total=np.empty(n, dtype=np.uint64), iters_max=np.empty(n, dtype=np.uint32))
+        _check(lib().bmpc_cl_get(self._h, n, _p(out["pose"]), _p(out["act"]), _p(out["u0"]), _p(out["target"]),
+                                 _p(out["idx"], _i32p), _p(out["iters_total"], C.POINTER(C.c_uint64)), _p(out["iters_max"], _u32p)))
+        return out
 
     # ---- trajectory point ---------------------------------------------------------------------------------------------------
     def extract_points(self, px, py, dx, dy, vel, dist, npoints=None, layout: str = "shared"):

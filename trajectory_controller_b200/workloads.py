@@ -158,3 +158,36 @@ def flops_setup(S: int, I: int, N: int) -> int:
 def flops_ctor(S: int, I: int, N: int) -> int:
     """Algorithmic flops of the constructor recursion (mpc.h:114-123), SURVEY.md §8(d)."""
     return N * (I * S * (2 * S - 1) + I * (2 * S - 1) + I + 2 * S * S * (2 * S - 1) + S)
+
+
+def sine_world_path(length_m: float = 70.0, ds: float = 0.1, amp: float = 0.3, period: float = 4.0):
+    """world path y(x) = amp*sin(2*pi*x/period) as a polyline with points every `ds`
+    metres of ARC LENGTH (positions and unit tangents, float64).  Returns (x, y, tx, ty)."""
+    k = 2 * math.pi / period
+    fine = np.linspace(0.0, length_m, int(length_m / ds) * 200 + 1)
+    dy = amp * k * np.cos(k * fine)
+    seg = np.sqrt(1.0 + dy * dy)
+    s = np.concatenate([[0.0], np.cumsum(0.5 * (seg[1:] + seg[:-1]) * np.diff(fine))])
+    marks = np.arange(0.0, s[-1], ds)
+    x = np.interp(marks, s, fine)
+    y = amp * np.sin(k * x)
+    t = amp * k * np.cos(k * x)
+    n = np.sqrt(1.0 + t * t)
+    return x, y, 1.0 / n, t / n
+
+
+def closed_loop_poses(count: int, seed: int = 45, path=None):
+    """Initial vehicle poses [count][4] = X, Y, cos(psi), sin(psi): lateral offset 0.3 U and heading offset 0.4 U
+    (drawn per vehicle in that order, like random_offsets_x0) around the start of the path."""
+    path = sine_world_path() if path is None else path
+    u = MT19937_64(seed).uniform(2 * count).reshape(count, 2)
+    psi0 = math.atan2(path[3][0], path[2][0])
+    psi = psi0 + 0.4 * u[:, 1]
+    # offset along the path normal at the start
+    nx, ny = -path[3][0], path[2][0]
+    pose = np.empty((count, 4))
+    pose[:, 0] = path[0][0] + 0.3 * u[:, 0] * nx
+    pose[:, 1] = path[1][0] + 0.3 * u[:, 0] * ny
+    pose[:, 2] = np.cos(psi)
+    pose[:, 3] = np.sin(psi)
+    return pose
