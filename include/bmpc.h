@@ -77,6 +77,11 @@ int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C,
  * dropping those terms is exact in IEEE arithmetic (only the sign of a zero can differ), so parity is unaffected.
  * enable = 0 forces the dense kernel (takes effect at the next bmpc_set_model).  Default: enabled. */
 int bmpc_set_specialization(bmpc_t* h, int enable);
+/* Two-stage solve (engine extension; default enabled).  When the shape offers it (horizon short enough for the
+ * controls and the linear term to live in registers), a solve runs as two kernels: stage A = set-up (mpc.h:258-266)
+ * plus the 50 coordinate steps (mpc.h:319-335), stage B = the projected-gradient phase (mpc.h:336-345) in a kernel
+ * specialised for it.  Results are bit-identical to the one-kernel solve; enable = 0 forces one kernel (A/B tests). */
+int bmpc_set_split(bmpc_t* h, int enable);
 /* Name of the pattern the current model runs with: "dense", "bicycle4", "tobi", "kat". */
 const char* bmpc_pattern_name(bmpc_t* h);
 /* mpc.h:190-214; defaults eps = 0.01, max_iterations = 10000 (mpc.h:103-104).  max_iterations saturates at 2^32-1. */

@@ -231,3 +231,56 @@ def test_extract_points_vs_oracle(oracle):
         # empty trajectory: default point (d,0),(1,0),0 with idx -1
         gi, gf, go = eng.extract_points(z[:0], z[:0], z[:0], z[:0], z[:0], np.float32([0.7]))
         assert gi[0] == -1 and gf[0] == 2 and go[0][0] == np.float32(0.7) and go[2][0] == 1.0
+
+
+# ------------------------------------------------------------------------------------------ two-stage solve
+@pytest.mark.parametrize("shape", ["bike30", "bike30_pim", "kat30", "tobi4", "dense427"])
+def test_split_solve_equals_one_kernel(shape):
+    """bmpc_set_split: stage A (set-up + coordinate phase) + stage B (projected-gradient kernel, pg_kernel.cuh) must
+    reproduce the one-kernel solve bit for bit — u0, the whole control sequence, iteration counts, status — for cold
+    and warm solves, shared and per-instance models, and when max_iterations cuts the projected-gradient phase."""
+    rng = np.random.default_rng(11)
+    if shape.startswith("bike30"):
+        m, N, B, scale = W.bicycle4_model(), 30, 3000, None
+    elif shape == "kat30":
+        m, N, B, scale = W.kat_model(), 30, 500, 3.0
+    elif shape == "tobi4":
+        m, N, B, scale = W.tobi_model(), 4, 500, 0.5
+    else:
+        A = rng.standard_normal((3, 3)) * 0.5 + np.eye(3)
+        m = W.Model(A, rng.standard_normal((3, 2)), rng.standard_normal(3) * 0.01, np.array([1.0, 2.0, 0.5]),
+                    np.array([0.1, 0.2]), np.array([-0.4, -0.3]), np.array([0.5, 0.3]))
+        N, B, scale = 7, 500, 1.0
+    S, I = m.S, m.I
+    x0 = W.random_offsets_x0(B, 3) if scale is None else rng.standard_normal((B, S)) * scale
+    model, pim = m, False
+    if shape == "bike30_pim":
+        pim = True
+        speeds = rng.uniform(0.5, 2.0, B)
+        ms = [W.bicycle4_model(v=float(v)) for v in speeds]
+        model = {k: np.stack([getattr(mm, k) for mm in ms]) for k in ("A", "B", "C", "Q", "R", "lower", "upper")}
+    res = []
+    for split in (True, False):
+        with BatchedMPC(S, I, N, B) as eng:
+            eng.set_split(split)
+            eng.set_model(model, per_instance=pim)
+            out = []
+            for max_iter in (10000, 120):
+                eng.set_options(0.01 if shape != "kat30" else 1e-6, max_iter)
+                u0, it, st = eng.solve(x0, keep_controls=True)
+                out += [u0.copy(), it.copy(), st.copy(), eng.get_controls(B)]
+            eng.set_options(0.01, 10000)
+            eng.reset()
+            x = x0.copy()
+            for k in range(4):                               # persistent controllers (warm start, v carried over)
+                u0, it, st = eng.solve(x, warm=True)
+                out += [u0.copy(), it.copy(), st.copy(), eng.get_controls(B)]
+                Am = m.A if not pim else model["A"]
+                x = (np.einsum("bij,bj->bi", Am, x) if pim else x @ m.A.T) + (u0 @ m.B.T if not pim else np.einsum("bij,bj->bi", model["B"], u0))
+            res.append(out)
+    assert any((o > 50).any() for o in res[0][1::4]), "the projected-gradient stage never ran"
+    for a, b in zip(*res):
+        if a.dtype == np.float64:
+            assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+        else:
+            assert np.array_equal(a, b)

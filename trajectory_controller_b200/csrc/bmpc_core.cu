@@ -147,6 +147,8 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(h->vstate.alloc_zero(c * h->NI * es, h->stream), "alloc v");
     chk(h->target_const.alloc_zero(c * S * es, h->stream), "alloc target");
     chk(h->queue.alloc_zero(64, h->stream), "alloc queue");
+    chk(h->mmstate.alloc_zero(c * h->NI * es, h->stream), "alloc mmstate");
+    chk(h->pg_list.alloc_zero(c * 4, h->stream), "alloc pg_list");
     chk(h->small.alloc_zero(8 * 4096, h->stream), "alloc small");
     h->pinned_bytes = 8 * 4096;
     chk(cudaHostAlloc(&h->pinned, h->pinned_bytes, cudaHostAllocDefault), "cudaHostAlloc");
@@ -163,7 +165,7 @@ void bmpc_destroy(bmpc_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
                       &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
-                      &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
+                      &h->mmstate, &h->pg_list, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : h->ex) b.release();
     if (h->pinned) cudaFreeHost(h->pinned);
@@ -187,6 +189,12 @@ int bmpc_set_specialization(bmpc_t* h, int enable)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_set_specialization: null handle");
     h->specialize = enable != 0;
+    return BMPC_OK;
+}
+int bmpc_set_split(bmpc_t* h, int enable)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_set_split: null handle");
+    h->split = enable != 0;
     return BMPC_OK;
 }
 const char* bmpc_pattern_name(bmpc_t* h) { return h && h->solve_ops ? h->solve_ops->pattern : ""; }

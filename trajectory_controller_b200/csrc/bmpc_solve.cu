@@ -184,7 +184,11 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     g.mA = h->mA.p; g.mB = h->mB.p; g.mC = h->mC.p; g.mQ = h->mQ.p; g.mR = h->mR.p; g.mlo = h->mlo.p; g.mhi = h->mhi.p;
     g.mlambda = h->mlambda.p; g.mqdiag = h->mqdiag.p;
     g.queue = (unsigned long long*)h->queue.p;
-    BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 8, h->stream));
+    // Two-stage solve (pg_kernel.cuh): needs the stage-B kernel for this shape, iterations beyond the 50 coordinate
+    // steps, and eps > 0 (stage B tests "|df| >= eps" instead of carrying max_df; bmpc_set_options enforces eps > 0).
+    const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0;
+    g.split = split; g.mmstate = h->mmstate.p; g.pg_list = (uint32_t*)h->pg_list.p;
+    BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;
     BMPC_CUDA(h->solve_ops->info(h->precision, h->mode, h->per_instance, &ki));
@@ -192,9 +196,17 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     long long need_ctas = (count + ki.block - 1) / ki.block;
     int grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
     BMPC_CUDA(h->solve_ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
+    h->launches++;
+    if (split) {
+        KernelInfo kp;
+        BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &kp));
+        need_ctas = (count + kp.block - 1) / kp.block;
+        grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
+        BMPC_CUDA(h->solve_ops->pg(h->precision, h->mode, h->per_instance, g, grid, h->stream));
+        h->launches++;
+    }
     BMPC_CUDA(cudaEventRecord(h->ev1, h->stream));
     h->timed = true;
-    h->launches++;
     if (warm && h->full_targets) h->head = h->head + 1 == h->N ? 0 : h->head + 1;   // mpc.h:236-237
     return BMPC_OK;
 }

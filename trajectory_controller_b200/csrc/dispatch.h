@@ -18,7 +18,9 @@ struct GenericSolve {
     const void* x0; void* controls; void* vstate; void* target; void* u0;
     uint32_t* iters; uint8_t* status;
     const void *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
-    unsigned long long* queue;
+    unsigned long long* queue;                   // 64 bytes: [0] stage-A claims, [1] stage-B list length, [2] stage-B claims
+    int split;                                   // run the two-stage solve (pg_kernel.cuh)
+    void* mmstate; uint32_t* pg_list;
 };
 
 // mpc.h:114-123 for `count` models held SoA [elem][stride] on the device.
@@ -38,6 +40,10 @@ struct ShapeOps {
     cudaError_t (*solve)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
     cudaError_t (*ctor)(int precision, int mode, const GenericCtor& g, cudaStream_t st);
     cudaError_t (*info)(int precision, int mode, int pim, KernelInfo* out);
+    // stage B of the split solve; has_pg == 0 when the shape keeps u[]/MM[] out of registers (long horizons)
+    int has_pg;
+    cudaError_t (*pg)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
+    cudaError_t (*pg_info)(int precision, int mode, int pim, KernelInfo* out);
 };
 
 }  // namespace bmpc

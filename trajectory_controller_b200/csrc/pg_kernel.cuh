@@ -1,0 +1,338 @@
+// Stage B of the split solve: the accelerated projected-gradient phase of dlib::mpc's solve_linear_mpc
+// (/root/reference/dlib_files/dlib/control/mpc.h:271-345 for iter >= 50) as its own persistent kernel.
+//
+// Why a second kernel.  A cold (4,1,30) solve of BASELINE config 2 runs 704 iterations on average: 50 greedy
+// coordinate steps (mpc.h:319-335) and ~650 projected-gradient steps (mpc.h:336-345).  The one-kernel solver
+// (solve_kernel.cuh) serves both phases — and the set-up pass — from one warp-wide loop, so every trip pays for the
+// arg-max bookkeeping the coordinate step needs, for the coordinate step's register-indexed selects and for a
+// separate sweep that re-reads the gradient to apply the projected-gradient update.  ncu (profiles/
+// r1_ncu_solve_v2_exact64_metrics.csv): FP64 instructions are only 49 % of the issued instructions and the issue
+// slots (57 % busy from two warps per scheduler) limit the FP64 pipe to 53 %.  Stage A (solve_kernel with
+// p.split) now stops at iter == 50, parks u / v / MM in HBM (720 B per instance, once) and appends the instance to
+// a work list; this kernel continues from there with a pass that contains nothing but the phase's own arithmetic:
+//
+//   * the stopping test (mpc.h:289-311) needs no arg-max here, only "is any free |df| >= eps": one DSETP per entry;
+//   * the update (mpc.h:339-344) is applied inside the backward sweep, as soon as df[i] exists, while the chain
+//     of the next horizon step is in flight (more independent FP64 work per warp).  It is provisional: the reference
+//     tests convergence BEFORE updating, so the old (u, v) of each entry are parked in the stash slots the backward
+//     sweep has just consumed, and a lane that turns out to have converged reports those;
+//   * shared-memory traffic is paired: the two Q-weighted rows of a step, and (u_old, v_old), move as one 128-bit
+//     access (layout [pair][lane][2], conflict-free), 5 LSU instructions per horizon step instead of 8.
+//
+// Arithmetic, rounding order and iteration counts are those of solve_kernel.cuh (same Ar<T,EXACT> policies, same
+// structural-pattern term dropping): the parity tests compare the two-stage result with the oracle bit for bit.
+#pragma once
+#include "solve_kernel.cuh"
+
+namespace bmpc {
+
+template <typename T> struct SmemIO;
+template <> struct SmemIO<double> {
+    __device__ __forceinline__ static void st2(unsigned a, double x, double y) { asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(x), "d"(y)); }
+    __device__ __forceinline__ static void ld2(unsigned a, double& x, double& y) { asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(a)); }
+    __device__ __forceinline__ static void st1(unsigned a, double x) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(x)); }
+    __device__ __forceinline__ static double ld1(unsigned a) { double x; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(a)); return x; }
+};
+template <> struct SmemIO<float> {
+    __device__ __forceinline__ static void st2(unsigned a, float x, float y) { asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y)); }
+    __device__ __forceinline__ static void ld2(unsigned a, float& x, float& y) { asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x), "=f"(y) : "r"(a)); }
+    __device__ __forceinline__ static void st1(unsigned a, float x) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(x)); }
+    __device__ __forceinline__ static float ld1(unsigned a) { float x; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(a)); return x; }
+};
+
+template <typename T, int S, int I, int N, bool PIM, typename PAT>
+struct PgLayout {
+    using L0 = Layout<T, S, I, N, PIM, PAT>;
+    static constexpr int NI = N * I;
+    // u[] and MM[] must both live in registers (fully unrolled horizon); longer horizons stay on the one-kernel path
+    static constexpr bool OK = L0::UREG && L0::MMREG;
+    static constexpr int SQ = L0::SQ;
+    // slots per horizon step: the Q*M stash of the forward sweep, later (u_old, v_old) per control entry; even, so
+    // that a step's slots are whole pairs
+    static constexpr int W = ((imax_c(SQ, 2 * I) + 1) / 2) * 2;
+    static constexpr int O_QM = 0;                       // pairs, element index always even
+    static constexpr int O_V = O_QM + N * W;             // Nesterov v, single elements
+    static constexpr int O_MODEL = O_V + NI;
+    static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
+    static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
+    static constexpr int FIT = kSmemMax / WARP_BYTES;
+#ifndef BMPC_PG_CAP_WARPS
+#define BMPC_PG_CAP_WARPS 8
+#endif
+    static constexpr int WARPS = imax_c(1, imin_c(FIT, BMPC_PG_CAP_WARPS));
+    static constexpr int THREADS = WARPS * 32;
+    static constexpr int SMEM_BYTES = WARPS * WARP_BYTES;
+    __host__ __device__ static constexpr int qslot(int r) { return popc_c(PAT::QNZ & ((1u << r) - 1u)); }
+};
+
+template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
+struct PgSolver {
+    using L = PgLayout<T, S, I, N, PIM, PAT>;
+    using L0 = typename L::L0;
+    using P = SolveParams<T, S, I, N>;
+    using A_ = Ar<T, EXACT>;
+    using IO = SmemIO<T>;
+    using Bits = typename BitsOf<T>::type;
+    static constexpr int NI = L::NI;
+    static constexpr int ES = int(sizeof(T));
+
+    const P& p;
+    const T* smodel;      // PIM: this lane's column of the model block (element e at smodel[e*32])
+    unsigned a1, a2;      // shared-window byte addresses of this lane's column: single elements / pairs
+    T u[NI], mm[NI];
+
+    __device__ __forceinline__ PgSolver(const P& p_, const T* smodel_, unsigned a1_, unsigned a2_) : p(p_), smodel(smodel_), a1(a1_), a2(a2_) {}
+
+    __device__ __forceinline__ T mA(int r, int k) const { if constexpr (PIM) return smodel[(L0::M_A + r * S + k) * 32]; else return p.A[r * S + k]; }
+    __device__ __forceinline__ T mB(int r, int j) const { if constexpr (PIM) return smodel[(L0::M_B + r * I + j) * 32]; else return p.B[r * I + j]; }
+    __device__ __forceinline__ T mQ(int r) const { if constexpr (PIM) return smodel[(L0::M_Q + r) * 32]; else return p.Q[r]; }
+    __device__ __forceinline__ T mR(int j) const { if constexpr (PIM) return smodel[(L0::M_R + j) * 32]; else return p.R[j]; }
+    __device__ __forceinline__ T mLo(int j) const { if constexpr (PIM) return smodel[(L0::M_LO + j) * 32]; else return p.lo[j]; }
+    __device__ __forceinline__ T mHi(int j) const { if constexpr (PIM) return smodel[(L0::M_HI + j) * 32]; else return p.hi[j]; }
+
+    // byte addresses: pair slot `e` (even element index) and single element `e`
+    __device__ __forceinline__ unsigned pair_addr(int e) const { return a2 + (unsigned)(e * 32 * ES); }
+    __device__ __forceinline__ unsigned elem_addr(int e) const { return a1 + (unsigned)(e * 32 * ES); }
+
+    __host__ __device__ static constexpr bool bit(unsigned m, int e) { return ((m >> e) & 1u) != 0u; }
+    __device__ __forceinline__ static void term(T& t, bool& have, bool nz, bool one, T coef, T z)
+    {
+        if (!nz) return;
+        if (one) t = have ? A_::add(t, z) : z;
+        else t = have ? A_::madd(t, coef, z) : A_::mul(coef, z);
+        have = true;
+    }
+    __device__ __forceinline__ bool dotA(int r, const T* z, T& t) const
+    {
+        bool have = false; t = T(0);
+#pragma unroll
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::ANZ, r * S + k), bit(PAT::AONE, r * S + k), mA(r, k), z[k]);
+        return have;
+    }
+    __device__ __forceinline__ bool dotAT(int r, const T* z, T& t) const
+    {
+        bool have = false; t = T(0);
+#pragma unroll
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::ANZ, k * S + r), bit(PAT::AONE, k * S + r), mA(k, r), z[k]);
+        return have;
+    }
+    __device__ __forceinline__ bool dotB(int r, const T* uu, T& t) const
+    {
+        bool have = false; t = T(0);
+#pragma unroll
+        for (int k = 0; k < I; ++k) term(t, have, bit(PAT::BNZ, r * I + k), bit(PAT::BONE, r * I + k), mB(r, k), uu[k]);
+        return have;
+    }
+    __device__ __forceinline__ bool dotBT(int j, const T* z, T& t) const
+    {
+        bool have = false; t = T(0);
+#pragma unroll
+        for (int k = 0; k < S; ++k) term(t, have, bit(PAT::BNZ, k * I + j), bit(PAT::BONE, k * I + j), mB(k, j), z[k]);
+        return have;
+    }
+    __device__ __forceinline__ static T add_opt(bool ha, T a, bool hb, T b) { return ha ? (hb ? A_::add(a, b) : a) : (hb ? b : T(0)); }
+
+    // One projected-gradient iteration: gradient (mpc.h:275-283), stopping test (mpc.h:289-311) and the provisional
+    // update (mpc.h:339-344).  Returns true when the reference would NOT break at mpc.h:310, i.e. the update stands.
+    __device__ __forceinline__ bool pass(T inv_lambda, T beta)
+    {
+        T m[S];
+        {
+            T u0v[I];
+#pragma unroll
+            for (int j = 0; j < I; ++j) u0v[j] = u[j];
+#pragma unroll
+            for (int r = 0; r < S; ++r) { T tb; const bool hb = dotB(r, u0v, tb); m[r] = hb ? tb : T(0); }     // mpc.h:275
+        }
+        T w[S];
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            if (i > 0) {
+                T ui[I], mn[S];
+#pragma unroll
+                for (int j = 0; j < I; ++j) ui[j] = u[i * I + j];
+#pragma unroll
+                for (int r = 0; r < S; ++r) {                                                                   // mpc.h:277
+                    T t1; const bool h1 = dotA(r, m, t1);
+                    T ad; const bool hb = dotB(r, ui, ad);
+                    mn[r] = add_opt(h1, t1, hb, ad);
+                }
+#pragma unroll
+                for (int r = 0; r < S; ++r) m[r] = mn[r];
+            }
+            T qs[L::W];
+#pragma unroll
+            for (int q = 0; q < L::W; ++q) qs[q] = T(0);
+#pragma unroll
+            for (int r = 0; r < S; ++r) {                                                                       // mpc.h:279
+                if (bit(PAT::QNZ, r)) {
+                    const T q = A_::mul(mQ(r), m[r]);
+                    if (i < N - 1) qs[L::qslot(r)] = q; else w[r] = q;
+                } else if (i == N - 1) w[r] = T(0);
+            }
+            if (i < N - 1) {
+#pragma unroll
+                for (int q = 0; q < (L::SQ + 1) / 2; ++q) IO::st2(pair_addr(L::O_QM + i * L::W + 2 * q), qs[2 * q], qs[2 * q + 1]);
+            }
+        }
+        bool notconv = false;
+        T lo_[I], hi_[I];
+#pragma unroll
+        for (int j = 0; j < I; ++j) { lo_[j] = mLo(j); hi_[j] = mHi(j); }
+#pragma unroll
+        for (int i = N - 1; i >= 0; --i) {
+#pragma unroll
+            for (int j = I - 1; j >= 0; --j) {
+                const int k = i * I + j;
+                T bt; const bool hbt = dotBT(j, w, bt);
+                const T uij = u[k];
+                const T dfv = A_::add(add_opt(true, mm[k], hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
+                // mpc.h:289-311 reduced to its outcome: some free entry has |df| >= eps.  |df| >= eps > 0 implies
+                // df != 0 and df is not a NaN, so the sign bit tells which bound could block it (mpc.h:296-299).
+                const bool big = absval(dfv) >= p.eps;
+                const bool neg = (BitsOf<T>::to(dfv) & ~BitsOf<T>::abs_mask) != 0;
+                const bool at_hi = uij >= hi_[j], at_lo = uij <= lo_[j];
+                notconv |= big & !(neg ? at_hi : at_lo);
+                // mpc.h:339-344 (v_old = v; v = clamp(u - 1/lambda*df); u = clamp(v + beta*(v - v_old)))
+                const T v_old = IO::ld1(elem_addr(L::O_V + k));
+                const T vn = clamp_m(A_::sub(uij, A_::mul(inv_lambda, dfv)), lo_[j], hi_[j]);
+                const T un = clamp_m(A_::madd(vn, beta, A_::sub(vn, v_old)), lo_[j], hi_[j]);
+                IO::st2(pair_addr(L::O_QM + i * L::W + 2 * j), uij, v_old);      // this step's stash is consumed
+                IO::st1(elem_addr(L::O_V + k), vn);
+                u[k] = un;
+            }
+            if (i > 0) {
+                T st[L::W];
+#pragma unroll
+                for (int q = 0; q < (L::SQ + 1) / 2; ++q) IO::ld2(pair_addr(L::O_QM + (i - 1) * L::W + 2 * q), st[2 * q], st[2 * q + 1]);
+                T wn[S];
+#pragma unroll
+                for (int r = 0; r < S; ++r) {                                                                   // mpc.h:281
+                    T t; const bool h = dotAT(r, w, t);
+                    const bool hq = bit(PAT::QNZ, r);
+                    wn[r] = add_opt(hq, hq ? st[L::qslot(r)] : T(0), h, t);
+                }
+#pragma unroll
+                for (int r = 0; r < S; ++r) w[r] = wn[r];
+            }
+        }
+        return notconv;
+    }
+};
+
+// grid = #SMs (persistent), block = PgLayout::THREADS, dynamic smem = PgLayout::SMEM_BYTES.
+// Work list: p.pg_list[0 .. p.queue[1]) written by stage A; p.queue[2] is this kernel's claim counter.
+template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
+__global__ void __launch_bounds__((PgLayout<T, S, I, N, PIM, PAT>::THREADS), 1)
+pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
+{
+    using L = PgLayout<T, S, I, N, PIM, PAT>;
+    using L0 = typename L::L0;
+    using A_ = Ar<T, EXACT>;
+    using SV = PgSolver<T, S, I, N, EXACT, PIM, PAT>;
+    using IO = SmemIO<T>;
+    constexpr int NI = L::NI;
+    constexpr unsigned FULL = 0xffffffffu;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    T* wbase = reinterpret_cast<T*>(smem_raw) + (size_t)warp * L::ELEMS * 32;
+    const unsigned wb = (unsigned)__cvta_generic_to_shared(wbase);
+    T* smodel = wbase + L::O_MODEL * 32 + lane;
+    SV sv(p, smodel, wb + (unsigned)lane * sizeof(T), wb + (unsigned)lane * 2u * sizeof(T));
+
+    const unsigned long long total = *reinterpret_cast<const volatile unsigned long long*>(p.queue + 1);
+    long long inst = -1;
+    bool need = true, active = false;
+    uint32_t iter = 0;
+    T lambda = p.lambda, inv_lambda = T(0), beta = T(0);
+    if constexpr (!PIM) {
+        inv_lambda = A_::div(T(1), lambda);                                                   // mpc.h:342
+        const T sq = A_::sqrt(lambda);
+        beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));                                // mpc.h:343
+    }
+#pragma unroll
+    for (int k = 0; k < NI; ++k) { sv.u[k] = T(0); sv.mm[k] = T(0); }
+
+    while (true) {
+        const unsigned needmask = __ballot_sync(FULL, need);
+        if (needmask) {
+            const int leader = __ffs(needmask) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(p.queue + 2, (unsigned long long)__popc(needmask));
+            base = __shfl_sync(FULL, base, leader);
+            if (need) {
+                need = false;
+                const unsigned long long my = base + __popc(needmask & ((1u << lane) - 1u));
+                if (my < total) {
+                    inst = (long long)p.pg_list[my]; active = true; iter = 50;
+#pragma unroll
+                    for (int k = 0; k < NI; ++k) {
+                        sv.u[k] = p.controls[(long long)k * p.stride + inst];
+                        sv.mm[k] = p.mmstate[(long long)k * p.stride + inst];
+                        IO::st1(sv.elem_addr(L::O_V + k), p.vstate[(long long)k * p.stride + inst]);
+                    }
+                    if constexpr (PIM) {
+#pragma unroll
+                        for (int e = 0; e < S * S; ++e) smodel[(L0::M_A + e) * 32] = p.mA[(long long)e * p.stride + inst];
+#pragma unroll
+                        for (int e = 0; e < S * I; ++e) smodel[(L0::M_B + e) * 32] = p.mB[(long long)e * p.stride + inst];
+#pragma unroll
+                        for (int e = 0; e < S; ++e) smodel[(L0::M_Q + e) * 32] = p.mQ[(long long)e * p.stride + inst];
+#pragma unroll
+                        for (int e = 0; e < I; ++e) {
+                            smodel[(L0::M_R + e) * 32] = p.mR[(long long)e * p.stride + inst];
+                            smodel[(L0::M_LO + e) * 32] = p.mlo[(long long)e * p.stride + inst];
+                            smodel[(L0::M_HI + e) * 32] = p.mhi[(long long)e * p.stride + inst];
+                        }
+                        lambda = p.mlambda[inst];
+                        inv_lambda = A_::div(T(1), lambda);
+                        const T sq = A_::sqrt(lambda);
+                        beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));
+                    }
+                } else { inst = -1; active = false; }
+            }
+        }
+        if (!__any_sync(FULL, active)) break;
+
+        const bool notconv = sv.pass(inv_lambda, beta);
+
+        if (active) {
+            bool finished = false, hit_max = false;
+            if (!notconv) finished = true;                                             // mpc.h:310-311, update discarded
+            else { ++iter; if (iter >= p.max_iter) { finished = true; hit_max = true; } }   // mpc.h:271
+            if (finished) {
+                p.iters[inst] = iter;
+                p.status[inst] = hit_max ? 1 : 0;
+                const bool wc = p.warm || p.keep_controls;
+                if (hit_max) {
+#pragma unroll
+                    for (int k = 0; k < NI; ++k) {
+                        if (k < I) p.u0[(long long)k * p.stride + inst] = sv.u[k];                        // mpc.h:239
+                        if (wc) p.controls[(long long)k * p.stride + inst] = sv.u[k];
+                        if (p.warm) p.vstate[(long long)k * p.stride + inst] = IO::ld1(sv.elem_addr(L::O_V + k));
+                    }
+                } else {
+                    // converged: the iterate and v the test was taken on are parked in the stash slots
+#pragma unroll
+                    for (int k = 0; k < NI; ++k) {
+                        T uo, vo;
+                        IO::ld2(sv.pair_addr(L::O_QM + (k / I) * L::W + 2 * (k % I)), uo, vo);
+                        if (k < I) p.u0[(long long)k * p.stride + inst] = uo;
+                        if (wc) p.controls[(long long)k * p.stride + inst] = uo;
+                        if (p.warm) p.vstate[(long long)k * p.stride + inst] = vo;
+                    }
+                }
+                if (p.warm && p.target_full) {                                          // mpc.h:236-237 on the ring
+                    int last = p.head + N - 1; if (last >= N) last -= N;
+#pragma unroll
+                    for (int r = 0; r < S; ++r)
+                        p.target[((long long)p.head * S + r) * p.stride + inst] =
+                            p.target[((long long)last * S + r) * p.stride + inst];
+                }
+                active = false; need = true;
+            }
+        }
+    }
+}
+
+}  // namespace bmpc

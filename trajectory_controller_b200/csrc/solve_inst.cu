@@ -5,6 +5,7 @@
 #include "ctor_kernel.cuh"
 #include "dispatch.h"
 #include "patterns.h"
+#include "pg_kernel.cuh"
 #include "solve_kernel.cuh"
 
 #ifndef BMPC_S
@@ -21,11 +22,9 @@ using PAT_ = typename pat::BMPC_PAT<S_, I_>::type;
 constexpr bool kDense = (PAT_::ANZ == DensePattern<S_, I_>::ANZ && PAT_::AONE == 0u && PAT_::BNZ == DensePattern<S_, I_>::BNZ &&
                          PAT_::BONE == 0u && PAT_::CNZ == DensePattern<S_, I_>::CNZ && PAT_::QNZ == DensePattern<S_, I_>::QNZ);
 
-template <typename T, bool EXACT, bool PIM>
-cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
+template <typename T, bool PIM>
+void fill_params(SolveParams<T, S_, I_, N_>& p, const GenericSolve& g)
 {
-    using L = Layout<T, S_, I_, N_, PIM, PAT_>;
-    SolveParams<T, S_, I_, N_> p;
     for (int e = 0; e < S_ * S_; ++e) p.A[e] = PIM ? T(0) : (T)g.A[e];
     for (int e = 0; e < S_ * I_; ++e) p.B[e] = PIM ? T(0) : (T)g.B[e];
     for (int e = 0; e < S_; ++e) { p.C[e] = PIM ? T(0) : (T)g.C[e]; p.Q[e] = PIM ? T(0) : (T)g.Q[e]; }
@@ -42,6 +41,15 @@ cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
     p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
     p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
     p.queue = g.queue;
+    p.split = g.split; p.mmstate = (T*)g.mmstate; p.pg_list = g.pg_list;
+}
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
+{
+    using L = Layout<T, S_, I_, N_, PIM, PAT_>;
+    SolveParams<T, S_, I_, N_> p;
+    fill_params<T, PIM>(p, g);
     auto kern = solve_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -59,6 +67,39 @@ cudaError_t info_solve(KernelInfo* out)
     out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
     out->local_bytes = (int)a.localSizeBytes;
     return cudaSuccess;
+}
+
+constexpr bool kHasPg = PgLayout<double, S_, I_, N_, false, PAT_>::OK && PgLayout<float, S_, I_, N_, false, PAT_>::OK;
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t launch_pg(const GenericSolve& g, int grid, cudaStream_t st)
+{
+    if constexpr (!kHasPg) return cudaErrorNotSupported;
+    else {
+        using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
+        SolveParams<T, S_, I_, N_> p;
+        fill_params<T, PIM>(p, g);
+        auto kern = pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
+        return cudaGetLastError();
+    }
+}
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t info_pg(KernelInfo* out)
+{
+    if constexpr (!kHasPg) return cudaErrorNotSupported;
+    else {
+        using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
+        cudaFuncAttributes a;
+        cudaError_t e = cudaFuncGetAttributes(&a, pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>);
+        if (e != cudaSuccess) return e;
+        out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
+        out->local_bytes = (int)a.localSizeBytes;
+        return cudaSuccess;
+    }
 }
 
 template <typename T, bool EXACT>
@@ -88,6 +129,10 @@ cudaError_t solve_entry(int precision, int mode, int pim, const GenericSolve& g,
 { BMPC_DISPATCH(launch_solve, g, grid, st); }
 cudaError_t info_entry(int precision, int mode, int pim, KernelInfo* out)
 { BMPC_DISPATCH(info_solve, out); }
+cudaError_t pg_entry(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st)
+{ BMPC_DISPATCH(launch_pg, g, grid, st); }
+cudaError_t pg_info_entry(int precision, int mode, int pim, KernelInfo* out)
+{ BMPC_DISPATCH(info_pg, out); }
 template <bool DENSE>
 cudaError_t ctor_entry_t(int precision, int mode, const GenericCtor& g, cudaStream_t st)
 {
@@ -108,6 +153,6 @@ cudaError_t ctor_entry(int precision, int mode, const GenericCtor& g, cudaStream
 extern const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT);
 const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT) = {
     S_, I_, N_, BMPC_STR(BMPC_PAT), PAT_::ANZ, PAT_::AONE, PAT_::BNZ, PAT_::BONE, PAT_::CNZ, PAT_::QNZ,
-    solve_entry, ctor_entry, info_entry};
+    solve_entry, ctor_entry, info_entry, kHasPg ? 1 : 0, pg_entry, pg_info_entry};
 
 }  // namespace bmpc

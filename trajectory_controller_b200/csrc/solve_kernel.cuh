@@ -64,7 +64,11 @@ struct SolveParams {
     uint8_t* status;     // [stride]
     // per-instance models, SoA [elem][stride]
     const T *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
-    unsigned long long* queue;   // next unclaimed instance
+    unsigned long long* queue;   // [0] next unclaimed instance; [1] length of pg_list; [2] stage B's claim counter
+    // split solve (pg_kernel.cuh): stage A parks an instance that reaches iter == 50 and appends it to pg_list
+    int split;
+    T* mmstate;          // [N*I][stride]  the linear term MM of mpc.h:266, handed from stage A to stage B
+    uint32_t* pg_list;   // [stride]
 };
 
 __host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n += int(x & 1u); x >>= 1; } return n; }
@@ -460,6 +464,18 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                 }
                 ++iter;
                 if (iter >= p.max_iter) { finished = true; hit_max = true; }   // mpc.h:271
+                else if (p.split && iter == 50) {
+                    // Hand over to stage B (pg_kernel.cuh): the projected-gradient phase continues there from
+                    // exactly this state — controls, v (set by mpc.h:331-334 one line above, or stale) and MM.
+#pragma unroll(SV::UNROLL_K)
+                    for (int k = 0; k < NI; ++k) {
+                        p.controls[(long long)k * p.stride + inst] = sv.getU(k);
+                        p.vstate[(long long)k * p.stride + inst] = sm[(L::O_V + k) * 32];
+                        p.mmstate[(long long)k * p.stride + inst] = sv.getMM(k);
+                    }
+                    p.pg_list[atomicAdd(p.queue + 1, 1ull)] = (uint32_t)inst;
+                    active = false; need = true;
+                }
             }
             if (finished) {
 #pragma unroll

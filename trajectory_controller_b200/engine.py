@@ -40,6 +40,7 @@ SIGNATURES = {
     "bmpc_version": (C.c_char_p, []),
     "bmpc_set_model": (C.c_int, [C.c_void_p] + [_dp] * 7 + [C.c_int, C.c_int64]),
     "bmpc_set_specialization": (C.c_int, [C.c_void_p, C.c_int]),
+    "bmpc_set_split": (C.c_int, [C.c_void_p, C.c_int]),
     "bmpc_pattern_name": (C.c_char_p, [C.c_void_p]),
     "bmpc_set_options": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64]),
     "bmpc_get_options": (C.c_int, [C.c_void_p, _dp, C.POINTER(C.c_uint64)]),
@@ -148,6 +149,10 @@ class BatchedMPC:
         """False: always run the dense kernel (effective at the next set_model)."""
         _check(lib().bmpc_set_specialization(self._h, int(enable)))
         return self
+
+    def set_split(self, enable: bool):
+        """Two-stage solve (coordinate phase kernel + projected-gradient kernel) on/off; results are identical."""
+        _check(lib().bmpc_set_split(self._h, int(enable)))
 
     def pattern_name(self) -> str:
         return lib().bmpc_pattern_name(self._h).decode()
