@@ -138,6 +138,7 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     h->stream = h->own_stream;
     chk(cudaEventCreate(&h->ev0), "cudaEventCreate");
     chk(cudaEventCreate(&h->ev1), "cudaEventCreate");
+    chk(cudaEventCreate(&h->ev_mid), "cudaEventCreate");
     const size_t c = (size_t)capacity, es = (size_t)h->elem;
     chk(h->x0.alloc_zero(c * S * es, h->stream), "alloc x0");
     chk(h->u0.alloc_zero(c * I * es, h->stream), "alloc u0");
@@ -171,6 +172,7 @@ void bmpc_destroy(bmpc_t* h)
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_mid) cudaEventDestroy(h->ev_mid);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }

@@ -60,7 +60,8 @@ struct bmpc_handle {
     const bmpc::ShapeOps* solve_ops;   // pattern-specialised unit chosen by bmpc_set_model for the current model
     cudaStream_t stream = nullptr;       // the stream calls run on (own_stream unless bmpc_set_stream borrowed one)
     cudaStream_t own_stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr;   // solve start / end / between stage A and stage B
+    bool timed_split = false;
     bool timed = false;
     int sm_count = 0;
     int64_t launches = 0;

@@ -197,7 +197,9 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     int grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
     BMPC_CUDA(h->solve_ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
     h->launches++;
+    h->timed_split = split;
     if (split) {
+        BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
         KernelInfo kp;
         BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &kp));
         need_ctas = (count + kp.block - 1) / kp.block;
@@ -251,6 +253,36 @@ int bmpc_last_kernel_ms(bmpc_t* h, float* ms)
     BMPC_CUDA(cudaSetDevice(h->device));
     BMPC_CUDA(cudaEventSynchronize(h->ev1));
     BMPC_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return BMPC_OK;
+}
+
+int bmpc_last_stage_ms(bmpc_t* h, float* stage_a_ms, float* stage_b_ms)
+{
+    if (!h || !stage_a_ms || !stage_b_ms) return fail(BMPC_E_INVALID, "bmpc_last_stage_ms: null argument");
+    if (!h->timed) return fail(BMPC_E_STATE, "bmpc_last_stage_ms: no solve launched yet");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(cudaEventSynchronize(h->ev1));
+    if (h->timed_split) {
+        BMPC_CUDA(cudaEventElapsedTime(stage_a_ms, h->ev0, h->ev_mid));
+        BMPC_CUDA(cudaEventElapsedTime(stage_b_ms, h->ev_mid, h->ev1));
+    } else {
+        BMPC_CUDA(cudaEventElapsedTime(stage_a_ms, h->ev0, h->ev1));
+        *stage_b_ms = 0.f;
+    }
+    return BMPC_OK;
+}
+
+int bmpc_pg_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* regs)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_pg_kernel_info: null handle");
+    if (!h->solve_ops->has_pg) return fail(BMPC_E_UNSUPPORTED, "bmpc_pg_kernel_info: this shape has no stage-B kernel (one-kernel solve)");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    KernelInfo ki;
+    BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &ki));
+    if (grid) *grid = h->sm_count;
+    if (block) *block = ki.block;
+    if (smem_bytes) *smem_bytes = ki.smem_bytes;
+    if (regs) *regs = ki.regs;
     return BMPC_OK;
 }
 

@@ -58,6 +58,8 @@ SIGNATURES = {
     "bmpc_sync": (C.c_int, [C.c_void_p]),
     "bmpc_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bmpc_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
+    "bmpc_last_stage_ms": (C.c_int, [C.c_void_p, _fp, _fp]),
+    "bmpc_pg_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
     "bmpc_launch_count": (C.c_int64, [C.c_void_p]),
     "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
     "bmpc_probe_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
@@ -253,6 +255,16 @@ class BatchedMPC:
         ms = C.c_float()
         _check(lib().bmpc_last_kernel_ms(self._h, C.byref(ms)))
         return ms.value
+
+    def last_stage_ms(self):
+        a, b = C.c_float(), C.c_float()
+        _check(lib().bmpc_last_stage_ms(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def pg_kernel_info(self):
+        v = [C.c_int() for _ in range(4)]
+        _check(lib().bmpc_pg_kernel_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("grid", "block", "smem_bytes", "regs"), (x.value for x in v)))
 
     def launch_count(self) -> int:
         return int(lib().bmpc_launch_count(self._h))
