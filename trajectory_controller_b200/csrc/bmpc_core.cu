@@ -149,7 +149,8 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(h->target_const.alloc_zero(c * S * es, h->stream), "alloc target");
     chk(h->queue.alloc_zero(64, h->stream), "alloc queue");
     chk(h->mmstate.alloc_zero(c * h->NI * es, h->stream), "alloc mmstate");
-    chk(h->pg_list.alloc_zero(c * 4, h->stream), "alloc pg_list");
+    h->pg_ring = 1; while (h->pg_ring < c + 65536) h->pg_ring <<= 1;   // > capacity + lanes in flight (tickets)
+    chk(h->pg_list.alloc_zero(h->pg_ring * 4, h->stream), "alloc pg_list");
     chk(h->small.alloc_zero(8 * 4096, h->stream), "alloc small");
     h->pinned_bytes = 8 * 4096;
     chk(cudaHostAlloc(&h->pinned, h->pinned_bytes, cudaHostAllocDefault), "cudaHostAlloc");
@@ -197,6 +198,7 @@ int bmpc_set_split(bmpc_t* h, int enable)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_set_split: null handle");
     h->split = enable != 0;
+    h->slice = enable != 2;
     return BMPC_OK;
 }
 const char* bmpc_pattern_name(bmpc_t* h) { return h && h->solve_ops ? h->solve_ops->pattern : ""; }

@@ -80,6 +80,8 @@ struct bmpc_handle {
     // state
     bmpc::DevBuf x0, u0, iters, status, controls, vstate, target_const, target_full, queue;
     bmpc::DevBuf mmstate, pg_list;   // split solve: stage A -> stage B hand-over (pg_kernel.cuh)
+    size_t pg_ring = 0;              // ring capacity (power of two >= cap)
+    bool slice = true;               // stage B may time-slice small batches
     bool split = true;               // bmpc_set_split; the two-stage solve is used whenever the shape offers it
     bool full_targets = false;
     int head = 0;

@@ -188,6 +188,8 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     // steps, and eps > 0 (stage B tests "|df| >= eps" instead of carrying max_df; bmpc_set_options enforces eps > 0).
     const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0;
     g.split = split; g.mmstate = h->mmstate.p; g.pg_list = (uint32_t*)h->pg_list.p;
+    g.pg_mask = (unsigned)(h->pg_ring - 1); g.pg_slice = h->slice;
+    if (split) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
     BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;

@@ -56,6 +56,9 @@ struct PgLayout {
     static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
+#ifndef BMPC_PG_SLICE
+#define BMPC_PG_SLICE 128
+#endif
 #ifndef BMPC_PG_CAP_WARPS
 #define BMPC_PG_CAP_WARPS 8
 #endif
@@ -240,10 +243,30 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     T* smodel = wbase + L::O_MODEL * 32 + lane;
     SV sv(p, smodel, wb + (unsigned)lane * sizeof(T), wb + (unsigned)lane * 2u * sizeof(T));
 
-    const unsigned long long total = *reinterpret_cast<const volatile unsigned long long*>(p.queue + 1);
+    // ---- work ring ------------------------------------------------------------------------------------------------
+    // p.pg_list is a ring of instance ids (capacity p.pg_mask + 1 >= the handle's capacity, empty slots hold kEmpty);
+    // queue[1] = tail (producers: stage A, and lanes of this kernel that park an instance), queue[2] = head
+    // (consumers), queue[3] = instances not finished yet.  A producer publishes its state with a fence BEFORE the
+    // ring entry; a consumer reads the entry, fences, and reads the state with L2 loads (ld.cg).
+    constexpr uint32_t kEmpty = 0xffffffffu;
+    constexpr int kSpinLimit = 1 << 24;
+    volatile unsigned long long* const q = p.queue;
+    volatile uint32_t* const ring = p.pg_list;
+    const unsigned mask = p.pg_mask;
+    // Time slicing.  Iteration counts are heavy-tailed (p99/p50 ~ 2) and unpredictable from the state at iter 50, and
+    // a 65,536-instance batch gives each of the 37,888 lanes fewer than two instances: with run-to-completion a long
+    // instance that happens to be claimed late finishes long after the rest.  When the batch is that small every warp
+    // parks its live lanes every kSlice passes (u -> controls, v -> vstate, iter -> iters; 484 B per instance) at the
+    // ring's tail and claims the oldest entries instead: all instances advance at the same rate, the long ones run
+    // from the start, and what is left at the end is re-packed into full warps.  Arithmetic is untouched — an
+    // instance simply continues in another lane.
+    constexpr int kSlice = BMPC_PG_SLICE;
+    const bool slicing = p.pg_slice && q[1] <= 4ull * gridDim.x * L::THREADS;
     long long inst = -1;
-    bool need = true, active = false;
+    bool need = true, waiting = false, active = false;
+    unsigned slot = 0;
     uint32_t iter = 0;
+    int since = 0, backoff = 0;
     T lambda = p.lambda, inv_lambda = T(0), beta = T(0);
     if constexpr (!PIM) {
         inv_lambda = A_::div(T(1), lambda);                                                   // mpc.h:342
@@ -254,50 +277,70 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     for (int k = 0; k < NI; ++k) { sv.u[k] = T(0); sv.mm[k] = T(0); }
 
     while (true) {
+        // ---------------- fetch: a lane without work takes a ticket (one aggregated atomicAdd per warp, never fails)
+        // and polls the ring slot the ticket names; tickets beyond the tail are reservations for instances that
+        // other warps will park later (time slicing) and are simply abandoned when nothing is left to finish.
         const unsigned needmask = __ballot_sync(FULL, need);
         if (needmask) {
             const int leader = __ffs(needmask) - 1;
-            unsigned long long base = 0;
-            if (lane == leader) base = atomicAdd(p.queue + 2, (unsigned long long)__popc(needmask));
-            base = __shfl_sync(FULL, base, leader);
-            if (need) {
-                need = false;
-                const unsigned long long my = base + __popc(needmask & ((1u << lane) - 1u));
-                if (my < total) {
-                    inst = (long long)p.pg_list[my]; active = true; iter = 50;
+            unsigned long long h = 0;
+            if (lane == leader) h = atomicAdd(p.queue + 2, (unsigned long long)__popc(needmask));
+            h = __shfl_sync(FULL, h, leader);
+            if (need) { slot = (unsigned)(h + (unsigned long long)__popc(needmask & ((1u << lane) - 1u))) & mask; need = false; waiting = true; }
+            backoff = 0;
+        }
+        if (__any_sync(FULL, waiting)) {
+            if (backoff > 0) --backoff;
+            else {
+            if (waiting) {
+                const uint32_t e = ring[slot];
+                if (e != kEmpty) {
+                // only a sliced run re-uses ring slots and reads state another warp of THIS launch has parked
+                if (slicing) { ring[slot] = kEmpty; __threadfence(); }
+                waiting = false;
+                inst = (long long)e; active = true;
+                iter = __ldcg(p.iters + inst);
 #pragma unroll
-                    for (int k = 0; k < NI; ++k) {
-                        sv.u[k] = p.controls[(long long)k * p.stride + inst];
-                        sv.mm[k] = p.mmstate[(long long)k * p.stride + inst];
-                        IO::st1(sv.elem_addr(L::O_V + k), p.vstate[(long long)k * p.stride + inst]);
+                for (int k = 0; k < NI; ++k) {
+                    sv.u[k] = __ldcg(p.controls + (long long)k * p.stride + inst);
+                    sv.mm[k] = __ldcg(p.mmstate + (long long)k * p.stride + inst);
+                    IO::st1(sv.elem_addr(L::O_V + k), __ldcg(p.vstate + (long long)k * p.stride + inst));
+                }
+                if constexpr (PIM) {
+#pragma unroll
+                    for (int e2 = 0; e2 < S * S; ++e2) smodel[(L0::M_A + e2) * 32] = p.mA[(long long)e2 * p.stride + inst];
+#pragma unroll
+                    for (int e2 = 0; e2 < S * I; ++e2) smodel[(L0::M_B + e2) * 32] = p.mB[(long long)e2 * p.stride + inst];
+#pragma unroll
+                    for (int e2 = 0; e2 < S; ++e2) smodel[(L0::M_Q + e2) * 32] = p.mQ[(long long)e2 * p.stride + inst];
+#pragma unroll
+                    for (int e2 = 0; e2 < I; ++e2) {
+                        smodel[(L0::M_R + e2) * 32] = p.mR[(long long)e2 * p.stride + inst];
+                        smodel[(L0::M_LO + e2) * 32] = p.mlo[(long long)e2 * p.stride + inst];
+                        smodel[(L0::M_HI + e2) * 32] = p.mhi[(long long)e2 * p.stride + inst];
                     }
-                    if constexpr (PIM) {
-#pragma unroll
-                        for (int e = 0; e < S * S; ++e) smodel[(L0::M_A + e) * 32] = p.mA[(long long)e * p.stride + inst];
-#pragma unroll
-                        for (int e = 0; e < S * I; ++e) smodel[(L0::M_B + e) * 32] = p.mB[(long long)e * p.stride + inst];
-#pragma unroll
-                        for (int e = 0; e < S; ++e) smodel[(L0::M_Q + e) * 32] = p.mQ[(long long)e * p.stride + inst];
-#pragma unroll
-                        for (int e = 0; e < I; ++e) {
-                            smodel[(L0::M_R + e) * 32] = p.mR[(long long)e * p.stride + inst];
-                            smodel[(L0::M_LO + e) * 32] = p.mlo[(long long)e * p.stride + inst];
-                            smodel[(L0::M_HI + e) * 32] = p.mhi[(long long)e * p.stride + inst];
-                        }
-                        lambda = p.mlambda[inst];
-                        inv_lambda = A_::div(T(1), lambda);
-                        const T sq = A_::sqrt(lambda);
-                        beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));
-                    }
-                } else { inst = -1; active = false; }
+                    lambda = p.mlambda[inst];
+                    inv_lambda = A_::div(T(1), lambda);
+                    const T sq = A_::sqrt(lambda);
+                    beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));
+                }
+                }
+            }
+            if (__any_sync(FULL, waiting)) backoff = 3;     // entries not there yet: poll again in four passes
             }
         }
-        if (!__any_sync(FULL, active)) break;
+        if (!__any_sync(FULL, active)) {
+            if (q[3] == 0) break;                             // every instance of the launch has finished
+            __nanosleep(1000); backoff = 0; since = 0;
+            continue;
+        }
 
         const bool notconv = sv.pass(inv_lambda, beta);
+        ++since;
 
+        bool finished = false;
         if (active) {
-            bool finished = false, hit_max = false;
+            bool hit_max = false;
             if (!notconv) finished = true;                                             // mpc.h:310-311, update discarded
             else { ++iter; if (iter >= p.max_iter) { finished = true; hit_max = true; } }   // mpc.h:271
             if (finished) {
@@ -330,6 +373,35 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                             p.target[((long long)last * S + r) * p.stride + inst];
                 }
                 active = false; need = true;
+            }
+        }
+        const unsigned finmask = __ballot_sync(FULL, finished);
+        if (finmask && lane == (__ffs(finmask) - 1)) atomicAdd(p.queue + 3, 0ull - (unsigned long long)__popc(finmask));
+
+        // ---------------- slice end: park the live lanes at the ring's tail -----------------------------------------
+        if (slicing && since >= kSlice) {
+            since = 0; backoff = 0;
+            const unsigned actmask = __ballot_sync(FULL, active);
+            if (actmask) {
+                if (active) {
+#pragma unroll
+                    for (int k = 0; k < NI; ++k) {
+                        p.controls[(long long)k * p.stride + inst] = sv.u[k];
+                        p.vstate[(long long)k * p.stride + inst] = IO::ld1(sv.elem_addr(L::O_V + k));
+                    }
+                    p.iters[inst] = iter;
+                    __threadfence();
+                }
+                const int leader = __ffs(actmask) - 1;
+                unsigned long long pos = 0;
+                if (lane == leader) pos = atomicAdd(p.queue + 1, (unsigned long long)__popc(actmask));
+                pos = __shfl_sync(FULL, pos, leader);
+                if (active) {
+                    const unsigned slot = (unsigned)(pos + (unsigned long long)__popc(actmask & ((1u << lane) - 1u))) & mask;
+                    for (int spin = 0; ring[slot] != kEmpty; ++spin) if (spin > kSpinLimit) __trap();
+                    ring[slot] = (uint32_t)inst;
+                    active = false; need = true; inst = -1;
+                }
             }
         }
     }

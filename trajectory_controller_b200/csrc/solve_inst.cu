@@ -41,7 +41,7 @@ void fill_params(SolveParams<T, S_, I_, N_>& p, const GenericSolve& g)
     p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
     p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
     p.queue = g.queue;
-    p.split = g.split; p.mmstate = (T*)g.mmstate; p.pg_list = g.pg_list;
+    p.split = g.split; p.mmstate = (T*)g.mmstate; p.pg_list = g.pg_list; p.pg_mask = g.pg_mask; p.pg_slice = g.pg_slice;
 }
 
 template <typename T, bool EXACT, bool PIM>

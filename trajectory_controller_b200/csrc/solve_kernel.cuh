@@ -64,11 +64,13 @@ struct SolveParams {
     uint8_t* status;     // [stride]
     // per-instance models, SoA [elem][stride]
     const T *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
-    unsigned long long* queue;   // [0] next unclaimed instance; [1] length of pg_list; [2] stage B's claim counter
+    unsigned long long* queue;   // [0] next unclaimed instance; [1] ring tail; [2] ring head; [3] instances stage B has not finished
     // split solve (pg_kernel.cuh): stage A parks an instance that reaches iter == 50 and appends it to pg_list
     int split;
     T* mmstate;          // [N*I][stride]  the linear term MM of mpc.h:266, handed from stage A to stage B
-    uint32_t* pg_list;   // [stride]
+    uint32_t* pg_list;   // ring of instance ids, capacity pg_mask + 1 (a power of two >= stride), 0xffffffff = empty
+    unsigned pg_mask;
+    int pg_slice;        // stage B may time-slice small batches (pg_kernel.cuh)
 };
 
 __host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n += int(x & 1u); x >>= 1; } return n; }
@@ -473,7 +475,9 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                         p.vstate[(long long)k * p.stride + inst] = sm[(L::O_V + k) * 32];
                         p.mmstate[(long long)k * p.stride + inst] = sv.getMM(k);
                     }
-                    p.pg_list[atomicAdd(p.queue + 1, 1ull)] = (uint32_t)inst;
+                    p.iters[inst] = iter;                                  // stage B resumes from here
+                    p.pg_list[(unsigned)atomicAdd(p.queue + 1, 1ull) & p.pg_mask] = (uint32_t)inst;
+                    atomicAdd(p.queue + 3, 1ull);                          // instances stage B still has to finish
                     active = false; need = true;
                 }
             }

@@ -152,8 +152,9 @@ class BatchedMPC:
         _check(lib().bmpc_set_specialization(self._h, int(enable)))
         return self
 
-    def set_split(self, enable: bool):
-        """Two-stage solve (coordinate phase kernel + projected-gradient kernel) on/off; results are identical."""
+    def set_split(self, enable):
+        """0/False: one-kernel solve; 1/True: two-stage solve (coordinate-phase kernel + projected-gradient kernel)
+        with time slicing of small batches (default); 2: two-stage without time slicing.  Results are identical."""
         _check(lib().bmpc_set_split(self._h, int(enable)))
 
     def pattern_name(self) -> str:
