@@ -103,6 +103,26 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------------- CPU legs
+def ncu_traffic(kernel_prefix: str, precision: int, mode: str, batch: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed `ncu --set full` capture of
+    this same command (profiles/r1_ncu_v4_exact64_metrics.csv: FP64 EXACT, 65,536 instances); None for other settings."""
+    if precision != 64 or mode != "exact" or batch != BATCH:
+        return None
+    path = os.path.join(ROOT, "profiles", "r1_ncu_v4_exact64_metrics.csv")
+    try:
+        import csv
+        rows = list(csv.reader(open(path)))
+        col = [i for i, name in enumerate(rows[0]) if kernel_prefix in name][0]
+        scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = 0.0
+        for r in rows[1:]:
+            if r[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(r[col]) * scale[r[1]]
+        return tot or None
+    except Exception:
+        return None
+
+
 def host_cores() -> int:
     try:
         return len(os.sched_getaffinity(0))
@@ -306,7 +326,9 @@ def run_ours(args):
                     "d2h_bytes_per_step": B * (I_ * 8 + 4 + 1), "api": "bmpc_solve (C ABI, pinned host buffers)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe", "achieved": achieved, "peak": peak_tf,
-                         "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": None,
+                         "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                         "traffic": ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", args.precision, args.mode, B),
+                         "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full, profiles/r1_ncu_v4_exact64_metrics.csv)",
                          "peak_source": "bmpc_probe_peak: register-resident FMA chains on this device (MEASURED_PEAKS.json "
                                         "holds only HBM and bf16-tensor figures; the solver uses neither)",
                          "peak_ginstr_fused": peak_gi, "peak_ginstr_unfused": peak_gi_unfused,
