@@ -194,6 +194,41 @@ int bmpc_cl_run(bmpc_t* h, int ticks);
 int bmpc_cl_get(bmpc_t* h, int64_t count, double* pose, double* act, double* u0, double* target, int32_t* idx,
                 uint64_t* iters_total, uint32_t* iters_max);
 
+/* ---- fleet tick: TrajectoryPointController::cycle(), tobiMPC branch, for `count` vehicles in one call ------------------
+ * Replaces, per vehicle, src/trajectory_point_follower.cpp:64-126 + :276-283 + mpcControllerTobi :301-389 (SURVEY.md
+ * §8(f) rank 1).  The handle must be a (2,2,N) controller (the reference uses N = MPC_HORIZON = 4).  Inputs, host arrays:
+ *   velocity[count]   car->velocity() (float);  |v| < 0.1 is replaced by 0.1 (:78-82)
+ *   v_model[count]    m_mpcLookupVelocity.linearSearch(v) (:323) evaluated by the caller (the lookup table lives in the
+ *                     un-vendored lms_math); NULL = use v itself
+ *   dist[count]       look-ahead distance (:66 lookup or :71 regelpunktMin + v*regelpunktSlope), evaluated by the caller
+ *   P, npoints, px..vel, strides   the TRAJECTORY polylines, exactly as for bmpc_extract_points
+ * On the device: getTrajectoryPoint (:392-443), phi_soll = atan2(dir.y, dir.x) and y_soll = position.y (:84-85), the
+ * per-vehicle model (:326-340) with bounds -+alpha_max (:16-18), a fresh dlib::mpc (constructor math mpc.h:114-123),
+ * set_target (:368-371), operator()((0,0)) (:374-377), the CarCommand fields (:114-125) and the crossing rule
+ * "targetSpeed < 0.5 -> steering 0" (:276-283).  Outputs, host arrays of `count`: steering_front / steering_rear
+ * (radians), target_speed (trajectoryPoint.velocity), target_distance (position.length(), float), state
+ * (BMPC_CAR_IDLE when the point's velocity is 0, else BMPC_CAR_DRIVING); optional (may be NULL): idx / flag of the
+ * selected polyline point, target[count][2] = (y_soll, phi_soll), iters.
+ * Parity: everything is bit-exact against the CPU restatement except atan2, which is CUDA's double atan2 (<= 2 ulp)
+ * where the reference calls libm's; the tests bound the effect (|d phi_soll| <= 4e-16, |d steering| <= 1e-9).
+ * The call replaces the handle's model, targets and controller state (fresh controllers every tick, like the
+ * reference, which constructs its dlib::mpc inside mpcControllerTobi). */
+#define BMPC_CAR_IDLE 0
+#define BMPC_CAR_DRIVING 1
+typedef struct bmpc_tick_config {
+    double T;                      /* mpcParameters.stepSize, :96 (0.1) */
+    double l;                      /* wheelbase, include/trajectory_point_follower.h:47 (0.21) */
+    double weight_y, weight_phi;   /* :92-93 (20, 7) */
+    double weight_steering_front, weight_steering_rear;   /* :94-95 (0.0005, 10) */
+    double alpha_max;              /* :16 (22*M_PI/180) */
+} bmpc_tick_config;
+int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_config* cfg, const float* velocity,
+                         const double* v_model, const float* dist, int P, const int32_t* npoints,
+                         const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                         int64_t stride_instance, int64_t stride_point, double* steering_front,
+                         double* steering_rear, float* target_speed, float* target_distance, uint8_t* state,
+                         int32_t* idx, uint8_t* flag, double* target, uint32_t* iters);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,14 @@ const ShapeOps* find_shape(int S, int I, int N)
     return nullptr;
 }
 
+// A named pattern unit of the shape (callers guarantee that the model satisfies it), or null.
+const ShapeOps* find_pattern(int S, int I, int N, const char* name)
+{
+    for (const ShapeOps* o : g_all_ops)
+        if (o->S == S && o->I == I && o->N == N && std::strcmp(o->pattern, name) == 0) return o;
+    return nullptr;
+}
+
 static int popcount_u(unsigned x) { int n = 0; while (x) { n += x & 1u; x >>= 1; } return n; }
 
 // A model (count instances, instance-major doubles already rounded to the compute type by `rnd`) satisfies a pattern

@@ -64,6 +64,8 @@ SIGNATURES = {
     "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
     "bmpc_probe_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "bmpc_extract_points": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
+    "bmpc_fleet_tick_tobi": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, _fp, _dp, _fp, C.c_int, _i32p] + [_fp] * 5 +
+                             [C.c_int64, C.c_int64, _dp, _dp, _fp, _fp, _u8p, _i32p, _u8p, _dp, _u32p]),
     "bmpc_cl_init": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p] + [_dp] * 6),
     "bmpc_cl_run": (C.c_int, [C.c_void_p, C.c_int]),
     "bmpc_cl_get": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _dp, _dp, _i32p, C.POINTER(C.c_uint64), _u32p]),
@@ -77,6 +79,16 @@ class ClConfig(C.Structure):
 
 
 _lib = None
+
+
+class TickConfig(C.Structure):
+    """bmpc_tick_config; defaults = the reference's (src/trajectory_point_follower.cpp:16,92-96, header :47)."""
+    _fields_ = [("T", C.c_double), ("l", C.c_double), ("weight_y", C.c_double), ("weight_phi", C.c_double),
+                ("weight_steering_front", C.c_double), ("weight_steering_rear", C.c_double), ("alpha_max", C.c_double)]
+
+    def __init__(self, T=0.1, l=0.21, weight_y=20.0, weight_phi=7.0, weight_steering_front=0.0005, weight_steering_rear=10.0,
+                 alpha_max=22 * 3.141592653589793 / 180):
+        super().__init__(T, l, weight_y, weight_phi, weight_steering_front, weight_steering_rear, alpha_max)
 
 
 class BmpcError(RuntimeError):
@@ -300,6 +312,34 @@ class BatchedMPC:
                    idx=np.empty(n, dtype=np.int32), iters_total=np.empty(n, dtype=np.uint64), iters_max=np.empty(n, dtype=np.uint32))
         _check(lib().bmpc_cl_get(self._h, n, _p(out["pose"]), _p(out["act"]), _p(out["u0"]), _p(out["target"]),
                                  _p(out["idx"], _i32p), _p(out["iters_total"], C.POINTER(C.c_uint64)), _p(out["iters_max"], _u32p)))
+        return out
+
+    # ---- fleet tick (TrajectoryPointController::cycle, tobiMPC branch, batched) ------------------------------------------
+    def fleet_tick_tobi(self, velocity, dist, px, py, dx, dy, vel, layout: str = "pb", v_model=None, npoints=None, cfg=None):
+        """One control tick for len(velocity) vehicles: returns a dict of CarCommand fields and diagnostics."""
+        cfg = cfg or TickConfig()
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+        velocity = np.ascontiguousarray(velocity, dtype=np.float32)
+        dist = np.ascontiguousarray(dist, dtype=np.float32)
+        B = velocity.shape[0]
+        if layout == "shared":
+            P, si, sp = arrs[0].shape[0], 0, 1
+        elif layout == "pb":
+            P, si, sp = arrs[0].shape[0], 1, B
+        elif layout == "bp":
+            P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
+        else:
+            raise ValueError(layout)
+        vm = None if v_model is None else _c64(v_model)
+        npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+        out = dict(steering_front=np.empty(B), steering_rear=np.empty(B), target_speed=np.empty(B, dtype=np.float32),
+                   target_distance=np.empty(B, dtype=np.float32), state=np.empty(B, dtype=np.uint8),
+                   idx=np.empty(B, dtype=np.int32), flag=np.empty(B, dtype=np.uint8), target=np.empty((B, 2)),
+                   iters=np.empty(B, dtype=np.uint32))
+        _check(lib().bmpc_fleet_tick_tobi(self._h, B, C.byref(cfg), _p(velocity, _fp), _p(vm), _p(dist, _fp), P, _p(npts, _i32p),
+                                          *[_p(a, _fp) for a in arrs], si, sp, _p(out["steering_front"]), _p(out["steering_rear"]),
+                                          _p(out["target_speed"], _fp), _p(out["target_distance"], _fp), _p(out["state"], _u8p),
+                                          _p(out["idx"], _i32p), _p(out["flag"], _u8p), _p(out["target"]), _p(out["iters"], _u32p)))
         return out
 
     # ---- trajectory point ---------------------------------------------------------------------------------------------------
