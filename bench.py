@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=BATCH, help="instances per GPU (default: the BASELINE config)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-fast", action="store_true", help="skip the FAST-mode (FMA) side measurement of an exact run")
     return ap.parse_args()
 
 
@@ -147,7 +148,16 @@ def cpu_baseline(sample: int, seed: int):
     cores = host_cores()
     x0 = W.random_offsets_x0(sample, seed)
     secs = run(W.bicycle4_model(), N_, x0, cores)
+    # p50 latency of ONE solve on one host core (BASELINE metric: "p50 solve latency"): 96 single-instance calls
+    lat = []
+    for k in range(96):
+        t1 = time.perf_counter()
+        run(W.bicycle4_model(), N_, x0[k:k + 1], 1)
+        lat.append(time.perf_counter() - t1)
+    lat = np.array(lat[16:]) * 1e6
     return {"value": sample / secs, "unit": UNIT, "cores": cores, "kind": kind, "seconds": secs,
+            "latency_us_single_solve": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                        "what": "one cold (4,1,30) solve on one host thread (incl. the ctypes call)"},
             "sample": f"the first {sample} instances of rank 0's batch (seed {seed}), one cold dlib::mpc<4,1,30> per "
                       f"instance, {cores} host threads over contiguous slices, g++ -O2 -ffp-contract=off"}
 
@@ -292,6 +302,28 @@ def run_ours(args):
             lat.append(time.perf_counter() - t1)
         lat = np.array(lat[10:]) * 1e6
 
+    # ---------------- side measurement: the same batch in FAST mode (FMA allowed), checked against this run -------
+    fast_mode = None
+    if args.mode == "exact" and not args.no_fast:
+        u0_exact = out[0].copy()
+        with torch.cuda.stream(stream):
+            with BatchedMPC(S_, I_, N_, B, args.precision, FAST, device=local) as fe:
+                fe.set_model(model); fe.set_stream(stream.cuda_stream); fe.upload_x0(px0.numpy())
+                for _ in range(2):
+                    fe.solve_resident_async(B)
+                fev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(min(K, 5))]
+                for a, b in fev:
+                    flush.zero_(); a.record(stream); fe.solve_resident_async(B); b.record(stream)
+                stream.synchronize()
+                fu0, fit, _ = fe.download(B)
+        fms = float(np.mean([a.elapsed_time(b) for a, b in fev]))
+        tol = 1e-6 if args.precision == 64 else 1e-3
+        du = np.abs(fu0 - u0_exact)
+        fast_mode = {"value_per_gpu": B / fms * 1e3, "unit": UNIT, "ms_per_step": fms, "max_abs_du0_vs_exact": float(du.max()),
+                     "tolerance": tol, "within_tolerance": bool(du.max() <= tol),
+                     "iteration_counts_equal_frac": float((fit.astype(np.int64) == iters).mean()),
+                     "what": "same batch, FMA contraction allowed (BMPC_MODE_FAST); north-star tolerance |du| <= 1e-6 (FP64) / 1e-3 (FP32)"}
+
     flops = float(W.flops_setup(S_, I_, N_) * B + W.flops_per_iteration(S_, I_, N_) * iters.sum())
     ms_launch = float(np.mean(step_ms))
     achieved_solve = flops / (ms_launch * 1e-3) / 1e12
@@ -346,6 +378,8 @@ def run_ours(args):
                            "max": int(iters.max()), "hit_max_iterations": int((status != 0).sum())},
             "latency_us_batch1": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
                                   "what": "one cold (4,1,30) solve through bmpc_solve incl. copies"}}
+    if fast_mode is not None:
+        line["fast_mode"] = fast_mode
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED)
     print(json.dumps(line), flush=True)
