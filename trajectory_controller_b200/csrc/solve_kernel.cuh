@@ -77,13 +77,16 @@ __host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n 
 __host__ __device__ constexpr int imax_c(int a, int b) { return a > b ? a : b; }
 __host__ __device__ constexpr int imin_c(int a, int b) { return a < b ? a : b; }
 
+#ifndef BMPC_UREG_MAX
+#define BMPC_UREG_MAX 64
+#endif
 template <typename T, int S, int I, int N, bool PIM, typename PAT>
 struct Layout {
     static constexpr int NI = N * I;
     static constexpr int WORDS = int(sizeof(T) / 4);
     // u[] in registers (fully unrolled horizon) when it costs at most 64 32-bit registers; the linear term MM[] too
     // when both together stay within 128
-    static constexpr bool UREG = (NI * WORDS <= 64);
+    static constexpr bool UREG = (NI * WORDS <= BMPC_UREG_MAX);
     static constexpr bool MMREG = UREG && (2 * NI * WORDS <= 128);
     // Per horizon step: one slot per Q-weighted state row (the Q*M stash of the forward sweep, read back by the
     // backward sweep) — and, once the backward sweep has consumed a step's stash, the same slots hold that step's
