@@ -380,7 +380,7 @@ def run_ours(args):
                                   "what": "one cold (4,1,30) solve through bmpc_solve incl. copies"}}
     if fast_mode is not None:
         line["fast_mode"] = fast_mode
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:                    # reported baseline: rank 0 at N = 1 only
         line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED)
     print(json.dumps(line), flush=True)
 

@@ -188,15 +188,24 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     // steps, and eps > 0 (stage B tests "|df| >= eps" instead of carrying max_df; bmpc_set_options enforces eps > 0).
     const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0;
     g.split = split; g.mmstate = h->mmstate.p; g.pg_list = (uint32_t*)h->pg_list.p;
-    g.pg_mask = (unsigned)(h->pg_ring - 1); g.pg_slice = h->slice;
+    g.pg_mask = (unsigned)(h->pg_ring - 1);
+    // time slicing pays when lanes get only a few instances each (pg_kernel.cuh); 8 warps x 32 lanes per SM are resident
+    g.pg_slice = h->slice && count <= 4ll * h->sm_count * 256;
     if (split) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
     BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;
     BMPC_CUDA(h->solve_ops->info(h->precision, h->mode, h->per_instance, &ki));
-    // persistent grid: one CTA per SM, never more CTAs than there are warps' worth of instances
-    long long need_ctas = (count + ki.block - 1) / ki.block;
-    int grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
+    // Persistent grid: one CTA per SM.  A batch that does not fill every warp is spread over all SMs, one warp per
+    // SM sub-partition first (a warp alone on its scheduler runs a pass in ~4 200 cycles, two share it at ~6 050 for
+    // both): each CTA lets only its first `warp_limit` warps take work.
+    const long long need_warps = (count + 31) / 32;
+    int grid = (int)(need_warps < h->sm_count ? need_warps : h->sm_count);
+    auto limit_for = [&](int warps_per_cta) {
+        const long long per = (need_warps + grid - 1) / grid;
+        return (int)(per < warps_per_cta ? per : warps_per_cta);
+    };
+    g.warp_limit_a = limit_for(ki.warps);
     BMPC_CUDA(h->solve_ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
     h->launches++;
     h->timed_split = split;
@@ -204,8 +213,7 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
         BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
         KernelInfo kp;
         BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &kp));
-        need_ctas = (count + kp.block - 1) / kp.block;
-        grid = (int)(need_ctas < h->sm_count ? need_ctas : h->sm_count);
+        g.warp_limit_b = limit_for(kp.warps);
         BMPC_CUDA(h->solve_ops->pg(h->precision, h->mode, h->per_instance, g, grid, h->stream));
         h->launches++;
     }

@@ -21,6 +21,7 @@ struct GenericSolve {
     unsigned long long* queue;                   // 64 bytes: [0] stage-A claims, [1] stage-B list length, [2] stage-B claims
     int split;                                   // run the two-stage solve (pg_kernel.cuh)
     void* mmstate; uint32_t* pg_list; unsigned pg_mask; int pg_slice;
+    int warp_limit_a, warp_limit_b;              // warps per CTA that take work in stage A / stage B
 };
 
 // mpc.h:114-123 for `count` models held SoA [elem][stride] on the device.

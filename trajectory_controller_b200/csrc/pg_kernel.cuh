@@ -238,6 +238,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp >= p.warp_limit) return;          // no block-wide barrier anywhere in this kernel
     T* wbase = reinterpret_cast<T*>(smem_raw) + (size_t)warp * L::ELEMS * 32;
     const unsigned wb = (unsigned)__cvta_generic_to_shared(wbase);
     T* smodel = wbase + L::O_MODEL * 32 + lane;
@@ -255,13 +256,14 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     const unsigned mask = p.pg_mask;
     // Time slicing.  Iteration counts are heavy-tailed (p99/p50 ~ 2) and unpredictable from the state at iter 50, and
     // a 65,536-instance batch gives each of the 37,888 lanes fewer than two instances: with run-to-completion a long
-    // instance that happens to be claimed late finishes long after the rest.  When the batch is that small every warp
+    // instance that happens to be claimed late finishes long after the rest.  When the batch is that small (host
+    // decision, bmpc_solve.cu) every warp
     // parks its live lanes every kSlice passes (u -> controls, v -> vstate, iter -> iters; 484 B per instance) at the
     // ring's tail and claims the oldest entries instead: all instances advance at the same rate, the long ones run
     // from the start, and what is left at the end is re-packed into full warps.  Arithmetic is untouched — an
     // instance simply continues in another lane.
     constexpr int kSlice = BMPC_PG_SLICE;
-    const bool slicing = p.pg_slice && q[1] <= 4ull * gridDim.x * L::THREADS;
+    const bool slicing = p.pg_slice != 0;      // decided by the host (uniform): batch <= 4 instances per resident lane
     long long inst = -1;
     bool need = true, waiting = false, active = false;
     unsigned slot = 0;

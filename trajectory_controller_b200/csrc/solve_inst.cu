@@ -50,6 +50,7 @@ cudaError_t launch_solve(const GenericSolve& g, int grid, cudaStream_t st)
     using L = Layout<T, S_, I_, N_, PIM, PAT_>;
     SolveParams<T, S_, I_, N_> p;
     fill_params<T, PIM>(p, g);
+    p.warp_limit = g.warp_limit_a;
     auto kern = solve_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -79,6 +80,7 @@ cudaError_t launch_pg(const GenericSolve& g, int grid, cudaStream_t st)
         using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
         SolveParams<T, S_, I_, N_> p;
         fill_params<T, PIM>(p, g);
+        p.warp_limit = g.warp_limit_b;
         auto kern = pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
         if (e != cudaSuccess) return e;

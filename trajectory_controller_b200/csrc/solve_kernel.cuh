@@ -70,6 +70,7 @@ struct SolveParams {
     T* mmstate;          // [N*I][stride]  the linear term MM of mpc.h:266, handed from stage A to stage B
     uint32_t* pg_list;   // ring of instance ids, capacity pg_mask + 1 (a power of two >= stride), 0xffffffff = empty
     unsigned pg_mask;
+    int warp_limit;      // warps of a CTA that take work (small batches are spread one warp per SM sub-partition first)
     int pg_slice;        // stage B may time-slice small batches (pg_kernel.cuh)
 };
 
@@ -341,6 +342,7 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp >= p.warp_limit) return;          // no block-wide barrier anywhere in this kernel
     T* sm = reinterpret_cast<T*>(smem_raw) + (size_t)warp * L::ELEMS * 32 + lane;
     SV sv(p, sm);
 
