@@ -106,10 +106,10 @@ class ClockSampler(threading.Thread):
 # ------------------------------------------------------------------------------------------------- CPU legs
 def ncu_traffic(kernel_prefix: str, precision: int, mode: str, batch: int):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed `ncu --set full` capture of
-    this same command (profiles/r1_ncu_v4_exact64_metrics.csv: FP64 EXACT, 65,536 instances); None for other settings."""
+    this same command (profiles/r1_ncu_v5_exact64_metrics.csv: FP64 EXACT, 65,536 instances); None for other settings."""
     if precision != 64 or mode != "exact" or batch != BATCH:
         return None
-    path = os.path.join(ROOT, "profiles", "r1_ncu_v4_exact64_metrics.csv")
+    path = os.path.join(ROOT, "profiles", "r1_ncu_v5_exact64_metrics.csv")
     try:
         import csv
         rows = list(csv.reader(open(path)))
@@ -298,7 +298,7 @@ def run_ours(args):
         one = (np.empty((1, I_)), np.empty(1, dtype=np.uint32), np.empty(1, dtype=np.uint8))
         for k in range(60):
             t1 = time.perf_counter()
-            eng.solve(x0[k:k + 1], out=one)
+            eng.solve(x0[k % B:k % B + 1], out=one)
             lat.append(time.perf_counter() - t1)
         lat = np.array(lat[10:]) * 1e6
 
@@ -360,7 +360,7 @@ def run_ours(args):
             "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe", "achieved": achieved, "peak": peak_tf,
                          "unit": "TFLOP/s", "frac": achieved / peak_tf,
                          "traffic": ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", args.precision, args.mode, B),
-                         "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full, profiles/r1_ncu_v4_exact64_metrics.csv)",
+                         "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full, profiles/r1_ncu_v5_exact64_metrics.csv)",
                          "peak_source": "bmpc_probe_peak: register-resident FMA chains on this device (MEASURED_PEAKS.json "
                                         "holds only HBM and bf16-tensor figures; the solver uses neither)",
                          "peak_ginstr_fused": peak_gi, "peak_ginstr_unfused": peak_gi_unfused,

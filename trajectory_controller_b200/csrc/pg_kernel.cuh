@@ -24,6 +24,11 @@
 #pragma once
 #include "solve_kernel.cuh"
 
+// Build-time experiment switch (profiles/r1_experiments.md row 16): keep the linear term MM in shared memory.
+#ifndef BMPC_PG_MM_SMEM
+#define BMPC_PG_MM_SMEM 0
+#endif
+
 namespace bmpc {
 
 template <typename T> struct SmemIO;
@@ -52,7 +57,8 @@ struct PgLayout {
     static constexpr int W = ((imax_c(SQ, 2 * I) + 1) / 2) * 2;
     static constexpr int O_QM = 0;                       // pairs, element index always even
     static constexpr int O_V = O_QM + N * W;             // Nesterov v, single elements
-    static constexpr int O_MODEL = O_V + NI;
+    static constexpr int O_MM = O_V + NI;                // linear term MM when it is kept out of registers (BMPC_PG_MM_SMEM)
+    static constexpr int O_MODEL = O_MM + (BMPC_PG_MM_SMEM ? NI : 0);
     static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
@@ -82,7 +88,9 @@ struct PgSolver {
     const P& p;
     const T* smodel;      // PIM: this lane's column of the model block (element e at smodel[e*32])
     unsigned a1, a2;      // shared-window byte addresses of this lane's column: single elements / pairs
-    T u[NI], mm[NI];
+    T u[NI], mm[BMPC_PG_MM_SMEM ? 1 : NI];
+    __device__ __forceinline__ T getMM(int k) const { if constexpr (BMPC_PG_MM_SMEM != 0) return IO::ld1(elem_addr(L::O_MM + k)); else return mm[k]; }
+    __device__ __forceinline__ void setMM(int k, T v) { if constexpr (BMPC_PG_MM_SMEM != 0) IO::st1(elem_addr(L::O_MM + k), v); else mm[k] = v; }
 
     __device__ __forceinline__ PgSolver(const P& p_, const T* smodel_, unsigned a1_, unsigned a2_) : p(p_), smodel(smodel_), a1(a1_), a2(a2_) {}
 
@@ -189,7 +197,7 @@ struct PgSolver {
                 const int k = i * I + j;
                 T bt; const bool hbt = dotBT(j, w, bt);
                 const T uij = u[k];
-                const T dfv = A_::add(add_opt(true, mm[k], hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
+                const T dfv = A_::add(add_opt(true, getMM(k), hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
                 // mpc.h:289-311 reduced to its outcome: some free entry has |df| >= eps.  |df| >= eps > 0 implies
                 // df != 0 and df is not a NaN, so the sign bit tells which bound could block it (mpc.h:296-299).
                 const bool big = absval(dfv) >= p.eps;
@@ -276,7 +284,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));                                // mpc.h:343
     }
 #pragma unroll
-    for (int k = 0; k < NI; ++k) { sv.u[k] = T(0); sv.mm[k] = T(0); }
+    for (int k = 0; k < NI; ++k) { sv.u[k] = T(0); sv.setMM(k, T(0)); }
 
     while (true) {
         // ---------------- fetch: a lane without work takes a ticket (one aggregated atomicAdd per warp, never fails)
@@ -305,7 +313,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
 #pragma unroll
                 for (int k = 0; k < NI; ++k) {
                     sv.u[k] = __ldcg(p.controls + (long long)k * p.stride + inst);
-                    sv.mm[k] = __ldcg(p.mmstate + (long long)k * p.stride + inst);
+                    sv.setMM(k, __ldcg(p.mmstate + (long long)k * p.stride + inst));
                     IO::st1(sv.elem_addr(L::O_V + k), __ldcg(p.vstate + (long long)k * p.stride + inst));
                 }
                 if constexpr (PIM) {
