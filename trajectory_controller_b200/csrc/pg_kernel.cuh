@@ -24,7 +24,8 @@
 #pragma once
 #include "solve_kernel.cuh"
 
-// Build-time experiment switch (profiles/r1_experiments.md row 16): keep the linear term MM in shared memory.
+// Build-time experiment switch (profiles/r1_experiments.md rows 16, 18): number of entries of the linear term MM kept in
+// shared memory instead of registers (0 = all in registers; >= N*I = all in shared memory).
 #ifndef BMPC_PG_MM_SMEM
 #define BMPC_PG_MM_SMEM 0
 #endif
@@ -58,7 +59,8 @@ struct PgLayout {
     static constexpr int O_QM = 0;                       // pairs, element index always even
     static constexpr int O_V = O_QM + N * W;             // Nesterov v, single elements
     static constexpr int O_MM = O_V + NI;                // linear term MM when it is kept out of registers (BMPC_PG_MM_SMEM)
-    static constexpr int O_MODEL = O_MM + (BMPC_PG_MM_SMEM ? NI : 0);
+    static constexpr int MM_S = imin_c(BMPC_PG_MM_SMEM, NI);     // MM[0 .. MM_S) in shared memory, the rest in registers
+    static constexpr int O_MODEL = O_MM + MM_S;
     static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
@@ -88,9 +90,9 @@ struct PgSolver {
     const P& p;
     const T* smodel;      // PIM: this lane's column of the model block (element e at smodel[e*32])
     unsigned a1, a2;      // shared-window byte addresses of this lane's column: single elements / pairs
-    T u[NI], mm[BMPC_PG_MM_SMEM ? 1 : NI];
-    __device__ __forceinline__ T getMM(int k) const { if constexpr (BMPC_PG_MM_SMEM != 0) return IO::ld1(elem_addr(L::O_MM + k)); else return mm[k]; }
-    __device__ __forceinline__ void setMM(int k, T v) { if constexpr (BMPC_PG_MM_SMEM != 0) IO::st1(elem_addr(L::O_MM + k), v); else mm[k] = v; }
+    T u[NI], mm[NI - L::MM_S > 0 ? NI - L::MM_S : 1];
+    __device__ __forceinline__ T getMM(int k) const { if (k < L::MM_S) return IO::ld1(elem_addr(L::O_MM + k)); else return mm[k - L::MM_S]; }
+    __device__ __forceinline__ void setMM(int k, T v) { if (k < L::MM_S) IO::st1(elem_addr(L::O_MM + k), v); else mm[k - L::MM_S] = v; }
 
     __device__ __forceinline__ PgSolver(const P& p_, const T* smodel_, unsigned a1_, unsigned a2_) : p(p_), smodel(smodel_), a1(a1_), a2(a2_) {}
 
