@@ -234,7 +234,7 @@ def test_extract_points_vs_oracle(oracle):
 
 
 # ------------------------------------------------------------------------------------------ two-stage solve
-@pytest.mark.parametrize("shape", ["bike30", "bike30_pim", "kat30", "tobi4", "dense427"])
+@pytest.mark.parametrize("shape", ["bike30", "bike30_pim", "bike60", "kat30", "tobi4", "dense427"])
 def test_split_solve_equals_one_kernel(shape):
     """bmpc_set_split: stage A (set-up + coordinate phase) + stage B (projected-gradient kernel, pg_kernel.cuh) must
     reproduce the one-kernel solve bit for bit — u0, the whole control sequence, iteration counts, status — for cold
@@ -242,6 +242,8 @@ def test_split_solve_equals_one_kernel(shape):
     rng = np.random.default_rng(11)
     if shape.startswith("bike30"):
         m, N, B, scale = W.bicycle4_model(), 30, 3000, None
+    elif shape == "bike60":                                   # controls / linear term resident in shared memory in stage B
+        m, N, B, scale = W.bicycle4_model(), 60, 700, None
     elif shape == "kat30":
         m, N, B, scale = W.kat_model(), 30, 500, 3.0
     elif shape == "tobi4":

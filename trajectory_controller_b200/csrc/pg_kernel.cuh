@@ -50,16 +50,19 @@ template <typename T, int S, int I, int N, bool PIM, typename PAT>
 struct PgLayout {
     using L0 = Layout<T, S, I, N, PIM, PAT>;
     static constexpr int NI = N * I;
-    // u[] and MM[] must both live in registers (fully unrolled horizon); longer horizons stay on the one-kernel path
-    static constexpr bool OK = L0::UREG && L0::MMREG;
+    // Short horizons keep u[] and MM[] in registers (fully unrolled horizon).  Long ones (N*I*sizeof(T) > 256 B) keep
+    // them in this lane's shared-memory column and run the same pass as a rolled loop.
+    static constexpr bool UREG = L0::UREG && L0::MMREG;
+    static constexpr bool OK = true;
     static constexpr int SQ = L0::SQ;
     // slots per horizon step: the Q*M stash of the forward sweep, later (u_old, v_old) per control entry; even, so
     // that a step's slots are whole pairs
     static constexpr int W = ((imax_c(SQ, 2 * I) + 1) / 2) * 2;
     static constexpr int O_QM = 0;                       // pairs, element index always even
     static constexpr int O_V = O_QM + N * W;             // Nesterov v, single elements
-    static constexpr int O_MM = O_V + NI;                // linear term MM when it is kept out of registers (BMPC_PG_MM_SMEM)
-    static constexpr int MM_S = imin_c(BMPC_PG_MM_SMEM, NI);     // MM[0 .. MM_S) in shared memory, the rest in registers
+    static constexpr int O_U = O_V + NI;                 // controls, when not in registers
+    static constexpr int O_MM = O_U + (UREG ? 0 : NI);   // linear term MM: entries [0, MM_S) live here, the rest in registers
+    static constexpr int MM_S = UREG ? imin_c(BMPC_PG_MM_SMEM, NI) : NI;
     static constexpr int O_MODEL = O_MM + MM_S;
     static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
@@ -73,6 +76,9 @@ struct PgLayout {
     static constexpr int WARPS = imax_c(1, imin_c(FIT, BMPC_PG_CAP_WARPS));
     static constexpr int THREADS = WARPS * 32;
     static constexpr int SMEM_BYTES = WARPS * WARP_BYTES;
+    static_assert(FIT >= 1, "horizon too long for the shared-memory resident layout");
+    static constexpr int UNR = UREG ? N : 2;             // horizon loops: full unroll keeps u[] / MM[] in registers
+    static constexpr int UNR_K = UREG ? NI : 2;
     __host__ __device__ static constexpr int qslot(int r) { return popc_c(PAT::QNZ & ((1u << r) - 1u)); }
 };
 
@@ -90,7 +96,9 @@ struct PgSolver {
     const P& p;
     const T* smodel;      // PIM: this lane's column of the model block (element e at smodel[e*32])
     unsigned a1, a2;      // shared-window byte addresses of this lane's column: single elements / pairs
-    T u[NI], mm[NI - L::MM_S > 0 ? NI - L::MM_S : 1];
+    T u[L::UREG ? NI : 1], mm[NI - L::MM_S > 0 ? NI - L::MM_S : 1];
+    __device__ __forceinline__ T getU(int k) const { if constexpr (L::UREG) return u[k]; else return IO::ld1(elem_addr(L::O_U + k)); }
+    __device__ __forceinline__ void setU(int k, T v) { if constexpr (L::UREG) u[k] = v; else IO::st1(elem_addr(L::O_U + k), v); }
     __device__ __forceinline__ T getMM(int k) const { if (k < L::MM_S) return IO::ld1(elem_addr(L::O_MM + k)); else return mm[k - L::MM_S]; }
     __device__ __forceinline__ void setMM(int k, T v) { if (k < L::MM_S) IO::st1(elem_addr(L::O_MM + k), v); else mm[k - L::MM_S] = v; }
 
@@ -153,17 +161,17 @@ struct PgSolver {
         {
             T u0v[I];
 #pragma unroll
-            for (int j = 0; j < I; ++j) u0v[j] = u[j];
+            for (int j = 0; j < I; ++j) u0v[j] = getU(j);
 #pragma unroll
             for (int r = 0; r < S; ++r) { T tb; const bool hb = dotB(r, u0v, tb); m[r] = hb ? tb : T(0); }     // mpc.h:275
         }
         T w[S];
-#pragma unroll
+#pragma unroll(L::UNR)
         for (int i = 0; i < N; ++i) {
             if (i > 0) {
                 T ui[I], mn[S];
 #pragma unroll
-                for (int j = 0; j < I; ++j) ui[j] = u[i * I + j];
+                for (int j = 0; j < I; ++j) ui[j] = getU(i * I + j);
 #pragma unroll
                 for (int r = 0; r < S; ++r) {                                                                   // mpc.h:277
                     T t1; const bool h1 = dotA(r, m, t1);
@@ -192,13 +200,13 @@ struct PgSolver {
         T lo_[I], hi_[I];
 #pragma unroll
         for (int j = 0; j < I; ++j) { lo_[j] = mLo(j); hi_[j] = mHi(j); }
-#pragma unroll
+#pragma unroll(L::UNR)
         for (int i = N - 1; i >= 0; --i) {
 #pragma unroll
             for (int j = I - 1; j >= 0; --j) {
                 const int k = i * I + j;
                 T bt; const bool hbt = dotBT(j, w, bt);
-                const T uij = u[k];
+                const T uij = getU(k);
                 const T dfv = A_::add(add_opt(true, getMM(k), hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
                 // mpc.h:289-311 reduced to its outcome: some free entry has |df| >= eps.  |df| >= eps > 0 implies
                 // df != 0 and df is not a NaN, so the sign bit tells which bound could block it (mpc.h:296-299).
@@ -212,7 +220,7 @@ struct PgSolver {
                 const T un = clamp_m(A_::madd(vn, beta, A_::sub(vn, v_old)), lo_[j], hi_[j]);
                 IO::st2(pair_addr(L::O_QM + i * L::W + 2 * j), uij, v_old);      // this step's stash is consumed
                 IO::st1(elem_addr(L::O_V + k), vn);
-                u[k] = un;
+                setU(k, un);
             }
             if (i > 0) {
                 T st[L::W];
@@ -285,8 +293,8 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         const T sq = A_::sqrt(lambda);
         beta = A_::div(A_::sub(sq, T(1)), A_::add(sq, T(1)));                                // mpc.h:343
     }
-#pragma unroll
-    for (int k = 0; k < NI; ++k) { sv.u[k] = T(0); sv.setMM(k, T(0)); }
+#pragma unroll(L::UNR_K)
+    for (int k = 0; k < NI; ++k) { sv.setU(k, T(0)); sv.setMM(k, T(0)); }
 
     while (true) {
         // ---------------- fetch: a lane without work takes a ticket (one aggregated atomicAdd per warp, never fails)
@@ -312,9 +320,9 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                 waiting = false;
                 inst = (long long)e; active = true;
                 iter = __ldcg(p.iters + inst);
-#pragma unroll
+#pragma unroll(L::UNR_K)
                 for (int k = 0; k < NI; ++k) {
-                    sv.u[k] = __ldcg(p.controls + (long long)k * p.stride + inst);
+                    sv.setU(k, __ldcg(p.controls + (long long)k * p.stride + inst));
                     sv.setMM(k, __ldcg(p.mmstate + (long long)k * p.stride + inst));
                     IO::st1(sv.elem_addr(L::O_V + k), __ldcg(p.vstate + (long long)k * p.stride + inst));
                 }
@@ -360,15 +368,16 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                 p.status[inst] = hit_max ? 1 : 0;
                 const bool wc = p.warm || p.keep_controls;
                 if (hit_max) {
-#pragma unroll
+#pragma unroll(L::UNR_K)
                     for (int k = 0; k < NI; ++k) {
-                        if (k < I) p.u0[(long long)k * p.stride + inst] = sv.u[k];                        // mpc.h:239
-                        if (wc) p.controls[(long long)k * p.stride + inst] = sv.u[k];
+                        const T uk = sv.getU(k);
+                        if (k < I) p.u0[(long long)k * p.stride + inst] = uk;                             // mpc.h:239
+                        if (wc) p.controls[(long long)k * p.stride + inst] = uk;
                         if (p.warm) p.vstate[(long long)k * p.stride + inst] = IO::ld1(sv.elem_addr(L::O_V + k));
                     }
                 } else {
                     // converged: the iterate and v the test was taken on are parked in the stash slots
-#pragma unroll
+#pragma unroll(L::UNR_K)
                     for (int k = 0; k < NI; ++k) {
                         T uo, vo;
                         IO::ld2(sv.pair_addr(L::O_QM + (k / I) * L::W + 2 * (k % I)), uo, vo);
@@ -396,9 +405,9 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
             const unsigned actmask = __ballot_sync(FULL, active);
             if (actmask) {
                 if (active) {
-#pragma unroll
+#pragma unroll(L::UNR_K)
                     for (int k = 0; k < NI; ++k) {
-                        p.controls[(long long)k * p.stride + inst] = sv.u[k];
+                        p.controls[(long long)k * p.stride + inst] = sv.getU(k);
                         p.vstate[(long long)k * p.stride + inst] = IO::ld1(sv.elem_addr(L::O_V + k));
                     }
                     p.iters[inst] = iter;
