@@ -41,6 +41,7 @@ if ROOT not in sys.path:
 
 from trajectory_controller_b200 import workloads as W  # noqa: E402
 
+_emit = None
 METRIC = "mpc_solves_per_sec_horizon30"
 UNIT = "solves/s"
 S_, I_, N_ = 4, 1, 30
@@ -188,7 +189,7 @@ def run_reference(args):
                                        f"{cores} host threads, one cold dlib::mpc<4,1,30> per instance"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------------- GPU arm
@@ -382,11 +383,19 @@ def run_ours(args):
         line["fast_mode"] = fast_mode
     if not args.no_cpu and world == 1:                    # reported baseline: rank 0 at N = 1 only
         line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED)
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def main():
     args = parse_args()
+    # stdout must carry exactly one JSON line: libraries (NCCL's version banner, torchrun notices) write to fd 1
+    # directly, so fd 1 is pointed at stderr for the whole run and the JSON line goes to the saved descriptor.
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+    def _emit(line: dict):
+        os.write(saved, (json.dumps(line) + "\n").encode())
     if args.impl == "reference":
         run_reference(args)
     else:

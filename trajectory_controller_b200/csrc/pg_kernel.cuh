@@ -281,6 +281,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     // from the start, and what is left at the end is re-packed into full warps.  Arithmetic is untouched — an
     // instance simply continues in another lane.
     constexpr int kSlice = BMPC_PG_SLICE;
+    const unsigned long long total0 = q[1];     // entries stage A handed over
     const bool slicing = p.pg_slice != 0;      // decided by the host (uniform): batch <= 4 instances per resident lane
     long long inst = -1;
     bool need = true, waiting = false, active = false;
@@ -306,7 +307,12 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
             unsigned long long h = 0;
             if (lane == leader) h = atomicAdd(p.queue + 2, (unsigned long long)__popc(needmask));
             h = __shfl_sync(FULL, h, leader);
-            if (need) { slot = (unsigned)(h + (unsigned long long)__popc(needmask & ((1u << lane) - 1u))) & mask; need = false; waiting = true; }
+            if (need) {
+                const unsigned long long t = h + (unsigned long long)__popc(needmask & ((1u << lane) - 1u));
+                slot = (unsigned)t & mask; need = false;
+                // without time slicing nothing is ever added behind stage A's entries: a ticket beyond them retires the lane
+                waiting = slicing || t < total0;
+            }
             backoff = 0;
         }
         if (__any_sync(FULL, waiting)) {
@@ -351,6 +357,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         }
         if (!__any_sync(FULL, active)) {
             if (q[3] == 0) break;                             // every instance of the launch has finished
+            if (!slicing && !__any_sync(FULL, waiting)) break;   // no ticket of this warp can be served any more
             __nanosleep(1000); backoff = 0; since = 0;
             continue;
         }
