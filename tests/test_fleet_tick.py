@@ -90,3 +90,23 @@ def test_fleet_tick_rejects_wrong_shape():
     with BatchedMPC(4, 1, 10, 8) as eng:
         with pytest.raises(BmpcError):
             eng.fleet_tick_tobi(np.ones(3, dtype=np.float32), np.ones(3, dtype=np.float32), z, z, z, z, z)
+
+
+def test_fleet_tick_ragged_and_empty_polylines(oracle):
+    """npoints per vehicle: 0 (empty TRAJECTORY -> the default point (d,0),(1,0), velocity 0: src/...:394-407 -> target 0,
+    IDLE, zero steering), 1 (only the fallback point) and short polylines that end before the look-ahead distance."""
+    from trajectory_controller_b200.engine import BatchedMPC
+    B, P, N = 600, 48, 4
+    px, py, dx, dy, vel, speed, dist = _fleet(B, P, 21)
+    npts = np.random.default_rng(2).integers(0, P + 1, B).astype(np.int32)
+    npts[:20] = 0; npts[20:40] = 1; npts[40:60] = 3
+    idx, flag, (ox, oy, odx, ody, ov) = oracle.extract(px, py, dx, dy, vel, dist, npoints=npts, layout="pb")
+    with BatchedMPC(2, 2, N, B) as eng:
+        got = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb", npoints=npts)
+    assert np.array_equal(got["idx"], idx) and np.array_equal(got["flag"], flag)
+    assert np.array_equal(got["target_speed"].view(np.uint32), ov.view(np.uint32))
+    empty = npts == 0
+    assert np.all(got["state"][empty] == 0) and np.all(got["steering_front"][empty] == 0) and np.all(got["steering_rear"][empty] == 0)
+    assert np.all(got["target"][empty] == 0) and np.all(got["iters"][empty] == 0)      # already converged: 0 iterations
+    assert np.array_equal(got["target_distance"][empty].view(np.uint32), dist[empty].view(np.uint32))   # |(d, 0)| = d
+    assert np.array_equal(got["target"][:, 0].view(np.uint64), oy.astype(np.float64).view(np.uint64))

@@ -319,3 +319,19 @@ def test_tolerance_modes_fast_and_fp32(oracle):
         assert du.mean() <= 1e-4 and du.max() <= 2e-2, (name, du.mean(), du.max())
         assert np.all(np.abs(u) <= np.float32(W.ALPHA_MAX) * (1 + 1e-6)) and np.all(st == 0)
         assert abs(it.mean() - ref_it.mean()) < 5.0
+
+
+def test_config3_one_million_instances_properties(oracle):
+    """BASELINE configs[2] at this rank's full size (1,048,576 cold instances, seed 43, FP64 EXACT; stage B runs without
+    time slicing at this size): spot check against the oracle, box feasibility, and the mirror symmetry x0 -> -x0."""
+    bike, N, B = W.bicycle4_model(), 30, 1 << 20
+    x0 = W.random_offsets_x0(B, 43)
+    with BatchedMPC(4, 1, N, B) as eng:
+        eng.set_model(bike)
+        u0, it, st = eng.solve(x0)
+        pick = np.random.default_rng(3).choice(B, 384, replace=False)
+        uo, _, ito, _ = oracle.batch_cold(bike, N, x0[pick], nthreads=8, want_controls=False)
+        assert same_values(u0[pick], uo) and np.array_equal(it[pick], ito)
+        assert np.all(np.abs(u0) <= W.ALPHA_MAX) and np.all(st == 0) and it.max() <= 10000
+        u1, it1, _ = eng.solve(-x0)
+        assert same_values(u1, -u0) and np.array_equal(it1, it)
