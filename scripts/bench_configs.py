@@ -6,6 +6,7 @@ DESIGN.md §8 quotes.  Sizes are this rank's shard of the config (the path shard
     python scripts/bench_configs.py tolerance [--batch 1048576]      # config 3: FP32 / FAST vs FP64 EXACT
     python scripts/bench_configs.py sweep     [--per-combo 1024]     # config 4: horizon x weight grid, per-instance models
     python scripts/bench_configs.py closed    [--vehicles 262144 --ticks 500]   # config 5
+    python scripts/bench_configs.py tick      [--vehicles 262144]               # the reference's own (2,2,4) cycle() tick, batched
 """
 from __future__ import annotations
 
@@ -103,15 +104,64 @@ def closed(args):
                       "iters_max": int(r["iters_max"].max()), "max_distance_to_path_m": float(d.max())}))
 
 
+def tick(args):
+    """The reference's own configuration: one tobiMPC cycle() tick (dlib::mpc<2,2,4>, fresh controller per tick) for a
+    fleet, through the host API (H2D of polylines and speeds, D2H of the CarCommand fields inside the timed region)."""
+    B, P = args.vehicles, 48
+    rng = np.random.default_rng(9)
+    s = np.arange(P, dtype=np.float64)[:, None] * 0.1
+    ang = rng.uniform(-0.3, 0.3, B)[None, :] + rng.uniform(-0.8, 0.8, B)[None, :] * s
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+    px, py = f(np.cumsum(0.1 * np.cos(ang), 0)), f(rng.uniform(-0.15, 0.15, B)[None, :] + np.cumsum(0.1 * np.sin(ang), 0))
+    dx, dy, vel = f(np.cos(ang)), f(np.sin(ang)), f(np.ones((P, B)))
+    speed = rng.uniform(0.2, 2.5, B).astype(np.float32)
+    dist = (np.float32(0.6) + speed * np.float32(0.1)).astype(np.float32)
+    with BatchedMPC(2, 2, 4, B, FP64, EXACT) as eng:
+        r = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel)
+        l0 = eng.launch_count(); t0 = time.perf_counter()
+        reps = 5
+        for _ in range(reps):
+            r = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel)
+        dt = (time.perf_counter() - t0) / reps
+        launches = (eng.launch_count() - l0) // reps
+        kernel_ms = eng.last_kernel_ms()
+    out = {"config": "reference drop-in shape: tobiMPC cycle() tick, dlib::mpc<2,2,4> fresh per tick, %d vehicles, P=%d points each, "
+                     "host buffers in and out (bmpc_fleet_tick_tobi), FP64 EXACT, one GPU" % (B, P),
+           "ticks_per_s_per_vehicle_batch": 1 / dt, "vehicle_ticks_per_s": B / dt, "ms_per_fleet_tick": dt * 1e3,
+           "solve_kernels_ms": kernel_ms, "kernel_launches_per_tick": int(launches), "iters_mean": float(r["iters"].mean()),
+           "h2d_bytes_per_tick": int(5 * P * B * 4 + 2 * B * 4), "d2h_bytes_per_tick": int(B * (8 + 8 + 4 + 4 + 1 + 4 + 1 + 16 + 4))}
+    # the reference's CPU cost for the same tick: constructor + cold solve of dlib::mpc<2,2,4> (the glue is negligible)
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from _oracle import DlibRef, Oracle
+        n = min(B, 200000)
+        v = np.where(np.abs(speed[:n].astype(np.float64)) < 0.1, 0.1, speed[:n].astype(np.float64))
+        Tv = 0.1 * v; Tvl = Tv / 0.21
+        A = np.zeros((n, 2, 2)); A[:, 0, 0] = 1; A[:, 0, 1] = Tv; A[:, 1, 1] = 1
+        Bm = np.zeros((n, 2, 2)); Bm[:, 0, 1] = Tv; Bm[:, 1, 0] = Tvl; Bm[:, 1, 1] = -Tvl
+        am = 22 * np.pi / 180
+        models = dict(A=A, B=Bm, C=np.zeros((n, 2)), Q=np.tile([20.0, 7.0], (n, 1)), R=np.tile([0.0005, 10.0], (n, 1)),
+                      lower=np.full((n, 2), -am), upper=np.full((n, 2), am))
+        cores = len(os.sched_getaffinity(0))
+        solver = DlibRef() if DlibRef.available() and DlibRef().supported(2, 2, 4) else Oracle()
+        secs = solver.batch_cold(models, 4, np.zeros((n, 2)), target=r["target"][:n], per_instance=True, nthreads=cores,
+                                 want_controls=False)[3 if isinstance(solver, Oracle) else 2]
+        out["cpu_baseline"] = {"vehicle_ticks_per_s": n / secs, "cores": cores, "kind": "reference" if not isinstance(solver, Oracle) else "port",
+                               "sample": "%d vehicles, constructor + cold solve only" % n}
+    except Exception as e:      # the CPU leg is informative only
+        out["cpu_baseline"] = {"error": str(e)}
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["tolerance", "sweep", "closed"])
+    ap.add_argument("what", choices=["tolerance", "sweep", "closed", "tick"])
     ap.add_argument("--batch", type=int, default=1048576)
     ap.add_argument("--per-combo", type=int, default=1024)
     ap.add_argument("--vehicles", type=int, default=262144)
     ap.add_argument("--ticks", type=int, default=500)
     a = ap.parse_args()
-    {"tolerance": tolerance, "sweep": sweep, "closed": closed}[a.what](a)
+    {"tolerance": tolerance, "sweep": sweep, "closed": closed, "tick": tick}[a.what](a)
 
 
 if __name__ == "__main__":
