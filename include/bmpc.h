@@ -80,7 +80,7 @@ int bmpc_set_specialization(bmpc_t* h, int enable);
 /* Two-stage solve (engine extension; default enabled).  When the shape offers it (horizon short enough for the
  * controls and the linear term to live in registers), a solve runs as two kernels: stage A = set-up (mpc.h:258-266)
  * plus the 50 coordinate steps (mpc.h:319-335), stage B = the projected-gradient phase (mpc.h:336-345) in a kernel
- * specialised for it.  For batches of at most four instances per resident lane, stage B also time-slices: every
+ * specialised for it.  For batches of one to four instances per resident lane, stage B also time-slices: every
  * 128 iterations a warp parks its instances at the tail of a work ring and resumes the oldest parked ones, so that
  * heavy-tailed iteration counts do not leave most lanes idle behind a few late long solves.  Results are
  * bit-identical to the one-kernel solve in every setting.  enable: 0 = one kernel, 1 = two-stage with time slicing

@@ -335,3 +335,27 @@ def test_config3_one_million_instances_properties(oracle):
         assert np.all(np.abs(u0) <= W.ALPHA_MAX) and np.all(st == 0) and it.max() <= 10000
         u1, it1, _ = eng.solve(-x0)
         assert same_values(u1, -u0) and np.array_equal(it1, it)
+
+
+def test_time_slicing_is_invisible():
+    """Stage B parks and resumes instances every 128 iterations when a batch gives each lane 1-4 instances
+    (bmpc_solve.cu).  65,536 and 100,000 instances with time slicing (split = 1), without (2) and on the one-kernel
+    path (0): u0, the control sequences, iteration counts and status must agree bit for bit, cold and warm."""
+    bike, N = W.bicycle4_model(), 30
+    for B in (65536, 100000):
+        x0 = W.random_offsets_x0(B, 7)
+        res = []
+        for split in (1, 2, 0):
+            with BatchedMPC(4, 1, N, B) as eng:
+                eng.set_split(split)
+                eng.set_model(bike)
+                u0, it, st = eng.solve(x0, keep_controls=True)
+                out = [u0.copy(), it.copy(), st.copy(), eng.get_controls(B)]
+                eng.reset()
+                u0, it, st = eng.solve(x0, warm=True)
+                u1, it1, st1 = eng.solve(x0 @ bike.A.T + u0 @ bike.B.T, warm=True)
+                res.append(out + [u0.copy(), it.copy(), u1.copy(), it1.copy(), eng.get_controls(B)])
+        assert (res[0][1] > 178).mean() > 0.5          # most instances were parked at least once
+        for other in res[1:]:
+            for a, b in zip(res[0], other):
+                assert np.array_equal(a.view(np.uint64) if a.dtype == np.float64 else a, b.view(np.uint64) if b.dtype == np.float64 else b)

@@ -190,7 +190,8 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     g.split = split; g.mmstate = h->mmstate.p; g.pg_list = (uint32_t*)h->pg_list.p;
     g.pg_mask = (unsigned)(h->pg_ring - 1);
     // time slicing pays when lanes get only a few instances each (pg_kernel.cuh); 8 warps x 32 lanes per SM are resident
-    g.pg_slice = h->slice && count <= 4ll * h->sm_count * 256;
+    // (measured, scripts/slice_threshold.py: +4..10 % between 1 and 4 instances per lane, -4 % below, neutral above)
+    g.pg_slice = h->slice && count > 1ll * h->sm_count * 256 && count <= 4ll * h->sm_count * 256;
     if (split) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
     BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
