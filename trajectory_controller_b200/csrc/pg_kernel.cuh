@@ -242,7 +242,7 @@ struct PgSolver {
 };
 
 // grid = #SMs (persistent), block = PgLayout::THREADS, dynamic smem = PgLayout::SMEM_BYTES.
-// Work list: p.pg_list[0 .. p.queue[1]) written by stage A; p.queue[2] is this kernel's claim counter.
+// Work: the ring p.pg_list filled by stage A (and, when time slicing, by this kernel's own parked lanes).
 template <typename T, int S, int I, int N, bool EXACT, bool PIM, typename PAT>
 __global__ void __launch_bounds__((PgLayout<T, S, I, N, PIM, PAT>::THREADS), 1)
 pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
@@ -274,15 +274,14 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     const unsigned mask = p.pg_mask;
     // Time slicing.  Iteration counts are heavy-tailed (p99/p50 ~ 2) and unpredictable from the state at iter 50, and
     // a 65,536-instance batch gives each of the 37,888 lanes fewer than two instances: with run-to-completion a long
-    // instance that happens to be claimed late finishes long after the rest.  When the batch is that small (host
-    // decision, bmpc_solve.cu) every warp
-    // parks its live lanes every kSlice passes (u -> controls, v -> vstate, iter -> iters; 484 B per instance) at the
-    // ring's tail and claims the oldest entries instead: all instances advance at the same rate, the long ones run
-    // from the start, and what is left at the end is re-packed into full warps.  Arithmetic is untouched — an
-    // instance simply continues in another lane.
+    // instance that happens to be claimed late finishes long after the rest.  For batches of 1-4 instances per lane
+    // (host decision, bmpc_solve.cu) every warp parks its live lanes every kSlice passes (u -> controls,
+    // v -> vstate, iter -> iters; 484 B per instance) at the ring's tail and takes tickets for the oldest entries
+    // instead: all instances advance at the same rate, the long ones run from the start, and what is left at the
+    // end is re-packed into full warps.  Arithmetic is untouched: an instance simply continues in another lane.
     constexpr int kSlice = BMPC_PG_SLICE;
     const unsigned long long total0 = q[1];     // entries stage A handed over
-    const bool slicing = p.pg_slice != 0;      // decided by the host (uniform): batch <= 4 instances per resident lane
+    const bool slicing = p.pg_slice != 0;       // decided by the host, uniform over the grid
     long long inst = -1;
     bool need = true, waiting = false, active = false;
     unsigned slot = 0;
