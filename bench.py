@@ -358,7 +358,11 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / K, "h2d_bytes_per_step": B * S_ * 8,
                     "d2h_bytes_per_step": B * (I_ * 8 + 4 + 1), "api": "bmpc_solve (C ABI, pinned host buffers)"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe", "achieved": achieved, "peak": peak_tf,
+            "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe",
+                         "bound_note": "neither 'hbm' nor 'tensor': the solver is chains of small dependent mat-vecs held on chip "
+                                       "(DRAM traffic < 0.2 % of peak, no dense contraction), bound by the CUDA-core FP pipe "
+                                       "(DESIGN.md 4.1, SURVEY.md 8(d))",
+                         "achieved": achieved, "peak": peak_tf,
                          "unit": "TFLOP/s", "frac": achieved / peak_tf,
                          "traffic": ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", args.precision, args.mode, B),
                          "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full, profiles/r1_ncu_v5_exact64_metrics.csv)",
