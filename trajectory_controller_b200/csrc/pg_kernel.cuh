@@ -24,10 +24,13 @@
 #pragma once
 #include "solve_kernel.cuh"
 
-// Build-time experiment switch (profiles/r1_experiments.md rows 16, 18): number of entries of the linear term MM kept in
-// shared memory instead of registers (0 = all in registers; >= N*I = all in shared memory).
+// Number of entries of the linear term MM kept in shared memory instead of registers when the horizon is
+// register-resident (profiles/r1_experiments.md rows 16, 18; 0 = all in registers), and the resident-warp cap.
 #ifndef BMPC_PG_MM_SMEM
-#define BMPC_PG_MM_SMEM 0
+#define BMPC_PG_MM_SMEM 23
+#endif
+#ifndef BMPC_PG_CAP_WARPS
+#define BMPC_PG_CAP_WARPS 8
 #endif
 
 namespace bmpc {
@@ -62,16 +65,20 @@ struct PgLayout {
     static constexpr int O_V = O_QM + N * W;             // Nesterov v, single elements
     static constexpr int O_U = O_V + NI;                 // controls, when not in registers
     static constexpr int O_MM = O_U + (UREG ? 0 : NI);   // linear term MM: entries [0, MM_S) live here, the rest in registers
-    static constexpr int MM_S = UREG ? imin_c(BMPC_PG_MM_SMEM, NI) : NI;
+    // Register-resident horizons may still keep the first BMPC_PG_MM_SMEM entries of MM in shared memory — 23 of 30
+    // take the (4,1,30) kernel from 255 registers with spills to 252 without (single-warp pass -6 %,
+    // profiles/r1_experiments.md row 18) — but only where that costs no resident warp.
+    static constexpr int MODEL_LEN = PIM ? L0::M_LEN : 0;
+    static constexpr int MM_TRY = imin_c(BMPC_PG_MM_SMEM, NI);
+    static constexpr int WARPS_PLAIN = imin_c(kSmemMax / ((O_MM + MODEL_LEN) * 32 * int(sizeof(T))), BMPC_PG_CAP_WARPS);
+    static constexpr int WARPS_TRY = imin_c(kSmemMax / ((O_MM + MM_TRY + MODEL_LEN) * 32 * int(sizeof(T))), BMPC_PG_CAP_WARPS);
+    static constexpr int MM_S = UREG ? (WARPS_TRY == WARPS_PLAIN ? MM_TRY : 0) : NI;
     static constexpr int O_MODEL = O_MM + MM_S;
     static constexpr int ELEMS = O_MODEL + (PIM ? L0::M_LEN : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
 #ifndef BMPC_PG_SLICE
 #define BMPC_PG_SLICE 128
-#endif
-#ifndef BMPC_PG_CAP_WARPS
-#define BMPC_PG_CAP_WARPS 8
 #endif
     static constexpr int WARPS = imax_c(1, imin_c(FIT, BMPC_PG_CAP_WARPS));
     static constexpr int THREADS = WARPS * 32;
