@@ -105,24 +105,16 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------------- CPU legs
-def ncu_traffic(kernel_prefix: str, precision: int, mode: str, batch: int):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed `ncu --set full` capture of
-    this same command (profiles/r1_ncu_v5_exact64_metrics.csv: FP64 EXACT, 65,536 instances); None for other settings."""
-    if precision != 64 or mode != "exact" or batch != BATCH:
-        return None
-    path = os.path.join(ROOT, "profiles", "r1_ncu_v5_exact64_metrics.csv")
+def ncu_traffic(kernel_prefix: str, build_id: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the `ncu --set full` capture
+    of THIS build running this command: profiles/ncu_traffic.json maps a build id (bmpc_version(): digest of the
+    kernel sources) to {kernel prefix: {"bytes": ..., "capture": file}}.  None when the running build has no capture."""
     try:
-        import csv
-        rows = list(csv.reader(open(path)))
-        col = [i for i, name in enumerate(rows[0]) if kernel_prefix in name][0]
-        scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-        tot = 0.0
-        for r in rows[1:]:
-            if r[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                tot += float(r[col]) * scale[r[1]]
-        return tot or None
+        table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        ent = table.get(build_id, {}).get(kernel_prefix)
+        return (float(ent["bytes"]), ent.get("capture")) if ent else (None, None)
     except Exception:
-        return None
+        return (None, None)
 
 
 def host_cores() -> int:
@@ -133,22 +125,51 @@ def host_cores() -> int:
 
 
 def cpu_solver():
-    """(kind, callable(model, N, x0, nthreads) -> seconds).  The one place bench.py executes oracle/."""
+    """(kind, callable(model, N, x0, nthreads) -> (seconds, u0, iters or None)).  The one place bench.py executes oracle/."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from _oracle import DlibRef, Oracle
     if DlibRef.available():
         ref = DlibRef()
         if ref.supported(S_, I_, N_):
-            return "reference", lambda m, N, x0, nt: ref.batch_cold(m, N, x0, nthreads=nt, want_controls=False)[2]
+            def run_ref(m, N, x0, nt):
+                u0, _, secs = ref.batch_cold(m, N, x0, nthreads=nt, want_controls=False)
+                return secs, u0, None                      # dlib::mpc keeps its iteration counter private (mpc.h:270)
+            return "reference", run_ref
     orc = Oracle()
-    return "port", lambda m, N, x0, nt: orc.batch_cold(m, N, x0, nthreads=nt, want_controls=False)[3]
+
+    def run_port(m, N, x0, nt):
+        u0, _, it, secs = orc.batch_cold(m, N, x0, nthreads=nt, want_controls=False)
+        return secs, u0, it
+    return "port", run_port
 
 
-def cpu_baseline(sample: int, seed: int):
+def oracle_iterations(x0, cores):
+    """Iteration counts of the C restatement (pinned bit-for-bit to the real header, tests/test_oracle.py) — the
+    checker for the GPU's iteration counts, which dlib::mpc itself does not expose."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _oracle import Oracle
+    u0, _, it, _ = Oracle().batch_cold(W.bicycle4_model(), N_, x0, nthreads=cores, want_controls=False)
+    return u0, it
+
+
+def cpu_baseline(sample: int, seed: int, gpu=None):
+    """The timed CPU leg; with `gpu` = (u0, iters) of the same batch from the engine (EXACT FP64 runs), the solutions
+    the CPU leg just computed become the in-run parity check of the bench line."""
     kind, run = cpu_solver()
     cores = host_cores()
     x0 = W.random_offsets_x0(sample, seed)
-    secs = run(W.bicycle4_model(), N_, x0, cores)
+    secs, u0_cpu, it_cpu = run(W.bicycle4_model(), N_, x0, cores)
+    parity = None
+    if gpu is not None:
+        gu0, git = gpu[0][:sample], gpu[1][:sample]
+        if it_cpu is None:
+            _, it_cpu = oracle_iterations(x0, cores)
+        du = np.abs(gu0 - u0_cpu)
+        parity = {"checked": int(sample), "max_abs_du0": float(du.max()), "u0_equal": bool(np.all(gu0 == u0_cpu)),
+                  "iterations_equal": bool(np.array_equal(git.astype(np.int64), it_cpu.astype(np.int64))),
+                  "source": "oracle/_ref (the reference's dlib::mpc)" if kind == "reference" else "oracle/ (C restatement)",
+                  "iterations_source": "oracle/liboracle.so (dlib::mpc hides its counter, mpc.h:270)",
+                  "what": "EXACT FP64 results of the timed batch vs the CPU leg's solutions of the same instances"}
     # p50 latency of ONE solve on one host core (BASELINE metric: "p50 solve latency"): 96 single-instance calls
     lat = []
     for k in range(96):
@@ -156,7 +177,7 @@ def cpu_baseline(sample: int, seed: int):
         run(W.bicycle4_model(), N_, x0[k:k + 1], 1)
         lat.append(time.perf_counter() - t1)
     lat = np.array(lat[16:]) * 1e6
-    return {"value": sample / secs, "unit": UNIT, "cores": cores, "kind": kind, "seconds": secs,
+    return parity, {"value": sample / secs, "unit": UNIT, "cores": cores, "kind": kind, "seconds": secs,
             "latency_us_single_solve": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
                                         "what": "one cold (4,1,30) solve on one host thread (incl. the ctypes call)"},
             "sample": f"the first {sample} instances of rank 0's batch (seed {seed}), one cold dlib::mpc<4,1,30> per "
@@ -178,7 +199,7 @@ def run_reference(args):
         run(model, N_, x0[: max(cores * 8, 256)], cores)
     t = 0.0
     for _ in range(args.steps):
-        t += run(model, N_, x0, cores)
+        t += run(model, N_, x0, cores)[0]
     val = sample * args.steps / t
     cfg = config_dict(args, world)
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -242,6 +263,9 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.Stream(device=dev)
 
+    from trajectory_controller_b200 import engine as _engine
+    ver = _engine.lib().bmpc_version().decode()
+    build_id = ver.split(" build ")[1].split(" ")[0] if " build " in ver else "unknown"
     eng = BatchedMPC(S_, I_, N_, B, args.precision, mode, device=local)
     eng.set_model(model)
     peak_tf, peak_gi = eng.probe_peak(args.precision, True)
@@ -268,7 +292,8 @@ def run_ours(args):
         barrier()
         step_ms = [a.elapsed_time(b) for a, b in ev]
         t_res = max_over_ranks(sum(step_ms) / 1e3)
-        _, iters, status = eng.download(B, out)
+        u0_timed, iters, status = eng.download(B, out)
+        u0_timed = u0_timed.copy()
         iters = iters.astype(np.int64)
         # per-stage device times of the two-stage solve (events inside libbmpc, three extra untimed solves)
         stage = []
@@ -282,17 +307,52 @@ def run_ours(args):
             info_b = None
 
         # ---------------- end-to-end leg: host buffers through bmpc_solve ------------------------------------------
+        # N > 1: plus the job's only collective, the final result gather: one NCCL all_gather each of
+        # u0 / iteration counts / status straight from the engine's result buffers in HBM, then a D2H of the gathered
+        # arrays into pinned host memory on every rank — every rank ends the step holding the whole job's results.
+        gather = None
+        if world > 1:
+            du0, dit, dst = (torch.as_tensor(v, device=dev) for v in eng.device_results())
+            g_u0 = torch.empty((world * I_, B), dtype=du0.dtype, device=dev)
+            g_it = torch.empty((world * B,), dtype=torch.int32, device=dev)
+            g_st = torch.empty((world * B,), dtype=torch.uint8, device=dev)
+            h_u0 = torch.empty((world * I_, B), dtype=du0.dtype).pin_memory()
+            h_it = torch.empty((world * B,), dtype=torch.int32).pin_memory()
+            h_st = torch.empty((world * B,), dtype=torch.uint8).pin_memory()
+
+            def gather():
+                dist.all_gather_into_tensor(g_u0, du0)
+                dist.all_gather_into_tensor(g_it, dit)
+                dist.all_gather_into_tensor(g_st, dst)
+                h_u0.copy_(g_u0, non_blocking=True); h_it.copy_(g_it, non_blocking=True); h_st.copy_(g_st, non_blocking=True)
         for _ in range(min(Wm, 3)):
             eng.solve(px0.numpy(), out=out)
+            if gather:
+                gather()
         barrier()
         t0 = time.perf_counter()
         for _ in range(K):
             eng.solve(px0.numpy(), out=out)
+            if gather:
+                gather()
         stream.synchronize()
         t_e2e_local = time.perf_counter() - t0
         barrier()
         t_e2e = max_over_ranks(t_e2e_local)
         clocks = sampler.result()
+        gather_info = None
+        if gather:
+            # the gathered copy must be what each rank computed: rank r's block equals its own results
+            ok = bool(np.array_equal(h_u0.numpy()[rank * I_:(rank + 1) * I_].T, out[0]) and
+                      np.array_equal(h_it.numpy()[rank * B:(rank + 1) * B].view(np.uint32), out[1]))
+            gev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
+            for a, b in gev:
+                a.record(stream); gather(); b.record(stream)
+            stream.synchronize()
+            gms = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in gev])))
+            gather_info = {"ms": gms, "bytes_per_rank_out": world * B * (I_ * du0.element_size() + 5),
+                           "own_block_matches": bool(max_over_ranks(0.0 if ok else 1.0) == 0.0),
+                           "what": "3 x ncclAllGather (u0, iters, status) from HBM + D2H of the gathered arrays, inside e2e"}
 
         # ---------------- single-solve latency through the ABI (batch of 1, cold) ----------------------------------
         lat = []
@@ -351,12 +411,17 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank != 0:
         return
+    traffic, traffic_src = (None, None)
+    if args.precision == 64 and args.mode == "exact" and B == BATCH:
+        traffic, traffic_src = ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", build_id)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": 1e3 * t_res / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic", "config": config_dict(args, world),
             "clocks": clocks,
-            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / K, "h2d_bytes_per_step": B * S_ * 8,
-                    "d2h_bytes_per_step": B * (I_ * 8 + 4 + 1), "api": "bmpc_solve (C ABI, pinned host buffers)"},
+            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / K, "h2d_bytes_per_step": world * B * S_ * 8,
+                    "d2h_bytes_per_step": world * B * (I_ * 8 + 4 + 1) * (1 + (world if world > 1 else 0)),
+                    "api": "bmpc_solve (C ABI, pinned host buffers)" + (" + final result gather (NCCL all_gather + D2H on every rank)" if world > 1 else ""),
+                    "gather": gather_info},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64_pipe" if args.precision == 64 else "fp32_pipe",
                          "bound_note": "neither 'hbm' nor 'tensor': the solver is chains of small dependent mat-vecs held on chip "
@@ -364,8 +429,8 @@ def run_ours(args):
                                        "(DESIGN.md 4.1, SURVEY.md 8(d))",
                          "achieved": achieved, "peak": peak_tf,
                          "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                         "traffic": ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", args.precision, args.mode, B),
-                         "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full, profiles/r1_ncu_v5_exact64_metrics.csv)",
+                         "traffic": traffic, "traffic_unit": "bytes of DRAM traffic per launch (ncu --set full of this build: " + str(traffic_src) + ")",
+                         "build_id": build_id,
                          "peak_source": "bmpc_probe_peak: register-resident FMA chains on this device (MEASURED_PEAKS.json "
                                         "holds only HBM and bf16-tensor figures; the solver uses neither)",
                          "peak_ginstr_fused": peak_gi, "peak_ginstr_unfused": peak_gi_unfused,
@@ -386,7 +451,10 @@ def run_ours(args):
     if fast_mode is not None:
         line["fast_mode"] = fast_mode
     if not args.no_cpu and world == 1:                    # reported baseline: rank 0 at N = 1 only
-        line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED)
+        check = (u0_timed, iters) if (args.mode == "exact" and args.precision == 64) else None
+        parity, line["cpu_baseline"] = cpu_baseline(args.cpu_sample or min(B, 32768), SEED, check)
+        if parity is not None:
+            line["parity"] = parity
     _emit(line)
 
 

@@ -56,6 +56,9 @@ typedef enum bmpc_status {
 
 /* per-instance status byte written by a solve */
 #define BMPC_ST_MAXITER 1u      /* the loop ended at max_iterations (mpc.h:271) instead of the eps test (mpc.h:310) */
+#define BMPC_ST_NONFINITE 2u    /* a NaN / inf reached the solve through x0, the targets or the model: the result follows
+                                   dlib's arithmetic for such inputs but is not a control to act on (the reference logs
+                                   isnan() of its outputs, src/trajectory_point_follower.cpp:100-103) */
 
 /* ---- lifetime ------------------------------------------------------------------------------------------- */
 /* 1 if the (S,I,N) template shape is instantiated (dlib::mpc is a compile-time template too, mpc.h:13-18). */
@@ -69,7 +72,9 @@ const char* bmpc_version(void);
 
 /* ---- model / options  (mpc.h:51-125, :172-214) ------------------------------------------------------------- */
 /* A[S*S] B[S*I] C[S] Q[S] R[I] lower[I] upper[I]; per_instance = 0: one model for every instance;
- * 1: `count` models, instance-major.  Runs the lambda / Q_diag recursion (mpc.h:114-123) on the device. */
+ * 1: `count` models, instance-major.  Runs the lambda / Q_diag recursion (mpc.h:114-123) on the device.
+ * dlib's requires clause (mpc.h:92-94: min(Q) >= 0, min(R) > 0, upper >= lower) and finiteness are checked for every
+ * instance: BMPC_E_INVALID instead of dlib's undefined behaviour. */
 int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C, const double* Q, const double* R,
                    const double* lower, const double* upper, int per_instance, int64_t count);
 /* Structural specialisation.  bmpc_set_model picks, among the kernels compiled for the shape, the one whose structural
@@ -83,8 +88,10 @@ int bmpc_set_specialization(bmpc_t* h, int enable);
  * specialised for it.  For batches of one to four instances per resident lane, stage B also time-slices: every
  * 128 iterations a warp parks its instances at the tail of a work ring and resumes the oldest parked ones, so that
  * heavy-tailed iteration counts do not leave most lanes idle behind a few late long solves.  Results are
- * bit-identical to the one-kernel solve in every setting.  enable: 0 = one kernel, 1 = two-stage with time slicing
- * (default), 2 = two-stage without time slicing (A/B tests). */
+ * bit-identical to the one-kernel solve in every setting.  enable: 0 = one kernel; 1 = two-stage with fairness slices,
+ * retirement of surplus warps near the end of a launch and, for models with lower == -upper, the symmetric-bound
+ * stage-B kernel (default); 2 = two-stage, every instance runs to completion in the lane that claimed it; 3 = like 1
+ * with the literal stage-B kernel whatever the bounds (2 and 3 exist for A/B tests). */
 int bmpc_set_split(bmpc_t* h, int enable);
 /* Name of the pattern the current model runs with: "dense", "bicycle4", "tobi", "kat". */
 const char* bmpc_pattern_name(bmpc_t* h);
@@ -122,6 +129,11 @@ int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0);            /* H2
 int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags);   /* kernel only, on the handle's stream */
 int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t* status);
 int bmpc_sync(bmpc_t* h);
+/* Device pointers of the last solve's results, for callers that keep them in HBM (a multi-GPU host gathers them with
+ * one collective): u0 as [I][capacity] of the handle's compute type (double or float), iters as uint32[capacity],
+ * status as uint8[capacity].  Valid until bmpc_destroy; written by every solve on the handle's stream.  Any pointer
+ * argument may be NULL. */
+int bmpc_device_results(bmpc_t* h, void** u0, void** iters, void** status);
 /* Run every later call of this handle on the caller's CUDA stream (a cudaStream_t passed as void*; NULL = back to
  * the handle's own stream).  Lets a host application order the engine with its own copies/events, and lets a
  * benchmark bracket launches with its own events.  The handle never destroys a borrowed stream. */
@@ -200,7 +212,8 @@ int bmpc_cl_get(bmpc_t* h, int64_t count, double* pose, double* act, double* u0,
  *   velocity[count]   car->velocity() (float);  |v| < 0.1 is replaced by 0.1 (:78-82)
  *   v_model[count]    m_mpcLookupVelocity.linearSearch(v) (:323) evaluated by the caller (the lookup table lives in the
  *                     un-vendored lms_math); NULL = use v itself
- *   dist[count]       look-ahead distance (:66 lookup or :71 regelpunktMin + v*regelpunktSlope), evaluated by the caller
+ *   dist[count]       look-ahead distance (:66 lookup or :71 regelpunktMin + v*regelpunktSlope) evaluated by the caller,
+ *                     or NULL (see below)
  *   P, npoints, px..vel, strides   the TRAJECTORY polylines, exactly as for bmpc_extract_points
  * On the device: getTrajectoryPoint (:392-443), phi_soll = atan2(dir.y, dir.x) and y_soll = position.y (:84-85), the
  * per-vehicle model (:326-340) with bounds -+alpha_max (:16-18), a fresh dlib::mpc (constructor math mpc.h:114-123),
@@ -212,7 +225,21 @@ int bmpc_cl_get(bmpc_t* h, int64_t count, double* pose, double* act, double* u0,
  * Parity: everything is bit-exact against the CPU restatement except atan2, which is CUDA's double atan2 (<= 2 ulp)
  * where the reference calls libm's; the tests bound the effect (|d phi_soll| <= 4e-16, |d steering| <= 1e-9).
  * The call replaces the handle's model, targets and controller state (fresh controllers every tick, like the
- * reference, which constructs its dlib::mpc inside mpcControllerTobi). */
+ * reference, which constructs its dlib::mpc inside mpcControllerTobi).
+ *
+ * Look-ups and the crossing clamp on the device:
+ *   dist == NULL      the look-ahead distance is evaluated per vehicle on the device: the BMPC_LOOKUP_DISTANCE table at
+ *                     car->velocity() (:66), or regelpunktMin + v*regelpunktSlope in FOH drive mode (:70-73,
+ *                     bmpc_fleet_set_drive_mode)
+ *   v_model == NULL   and a BMPC_LOOKUP_VELOCITY table is set: m_mpcLookupVelocity.linearSearch(v) (:323) on the device
+ *   the "stop at crossing" clamp at the end of getTrajectoryPoint (:445-473) runs on the device after the extraction,
+ *   with one slowDownCar PID per vehicle resident in HBM across ticks; it is ON by default with the reference's config
+ *   defaults (bmpc_fleet_set_crossing).  target_speed is the clamped trajectoryPoint.velocity.
+ * sensor_utils::PID and lms::math::LookupTable are not vendored by the reference (parity unpinned); the semantics adopted,
+ * all in float with every operation rounded on its own, are those of the headless shim the module is built against:
+ *   PID::pid(e):   integral += e*dt;  deriv = first ? 0 : (e - prev)/dt;  prev = e;  Kp*e + Ki*integral + Kd*deriv
+ *   linearSearch:  n == 0 -> x;  x <= vx[0] -> vy[0];  first i with x <= vx[i] ->
+ *                  vy[i-1] + (vy[i]-vy[i-1])*(x-vx[i-1])/(vx[i]-vx[i-1]);  else vy[n-1] */
 #define BMPC_CAR_IDLE 0
 #define BMPC_CAR_DRIVING 1
 typedef struct bmpc_tick_config {
@@ -228,6 +255,49 @@ int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_config* cfg, 
                          int64_t stride_instance, int64_t stride_point, double* steering_front,
                          double* steering_rear, float* target_speed, float* target_distance, uint8_t* state,
                          int32_t* idx, uint8_t* flag, double* target, uint32_t* iters);
+
+/* lms::math::LookupTable<float, ASC> (include/trajectory_point_follower.h:33-34; filled by configsChanged(),
+ * src/...:292-295): n samples, vx ascending.  linearSearch = piecewise-linear, clamped at both ends; n = 0 removes the
+ * table (identity, like an unconfigured table). */
+#define BMPC_LOOKUP_DISTANCE 0   /* m_trajectoryPointDistanceLookup, src/...:66, :216 */
+#define BMPC_LOOKUP_VELOCITY 1   /* m_mpcLookupVelocity, src/...:323 */
+int bmpc_set_lookup(bmpc_t* h, int which, int n, const float* vx, const float* vy);
+/* Evaluates a table for `count` host floats on the device (what the fleet tick does internally; exposed for tests and
+ * for callers that want the look-ahead distances back). */
+int bmpc_lookup(bmpc_t* h, int which, int64_t count, const float* x, float* y);
+/* phxService->driveMode() == FOH (src/...:70-73): look-ahead = regelpunkt_min + v * regelpunkt_slope (defaults 0.6, 0.1)
+ * instead of the distance table. */
+int bmpc_fleet_set_drive_mode(bmpc_t* h, int foh, float regelpunkt_min, float regelpunkt_slope);
+
+/* The crossing clamp, src/...:445-473.  cfg == NULL switches it off (trajectoryPoint.velocity is the polyline's). */
+typedef struct bmpc_crossing_config {
+    float max_velocity_crossing;   /* "maxVelocityCrossing" 1.0   (:446, :452) */
+    float stopping_distance;       /* "stoppingDistance"    0.35  (:449) */
+    float distance_to_stop;        /* "distanceToStop"      1     (:450) */
+    float crossing_safety_zone;    /* "crossingSaftyZone"   0.05  (:457) */
+} bmpc_crossing_config;
+int bmpc_fleet_set_crossing(bmpc_t* h, const bmpc_crossing_config* cfg);
+/* The three sensor_utils::PID members (include/trajectory_point_follower.h:40-42), one state per vehicle each.
+ * set = PID::set(Kp, Ki, Kd, dt) (src/...:296-298; defaults slowDownCar 1,0,0,0.01; front / rear 1,1,0,0.01);
+ * reset = PID::reset() for every vehicle.  get/put move the states [count] (integral, prev, first) for tests and
+ * checkpoints; any pointer may be NULL. */
+#define BMPC_PID_SLOWDOWN 0
+#define BMPC_PID_FRONT 1
+#define BMPC_PID_REAR 2
+int bmpc_fleet_set_pid(bmpc_t* h, int which, float kp, float ki, float kd, float dt);
+int bmpc_fleet_reset_pid(bmpc_t* h, int which);
+int bmpc_fleet_get_pid(bmpc_t* h, int which, int64_t count, float* integral, float* prev, uint8_t* first);
+int bmpc_fleet_put_pid(bmpc_t* h, int which, int64_t count, const float* integral, const float* prev, const uint8_t* first);
+
+/* The non-MPC branch of cycle() (src/...:214-225, config type neither tobiMPC nor mikMPC) for `count` vehicles:
+ * look-ahead (dist or the table, as above) -> getTrajectoryPoint incl. the crossing clamp -> steering_front =
+ * pidControllerFront.pid(position.y), steering_rear = pidControllerRear.pid(directory.angle()), target_speed,
+ * target_distance, then the rule of :276-283.  Works on any handle (no MPC shape involved); the PID states persist in
+ * HBM across ticks.  idx / flag may be NULL.  directory.angle() is atan2f on the device (<= 2 ulp against libm). */
+int bmpc_fleet_tick_pid(bmpc_t* h, int64_t count, const float* velocity, const float* dist, int P, const int32_t* npoints,
+                        const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                        int64_t stride_instance, int64_t stride_point, double* steering_front, double* steering_rear,
+                        float* target_speed, float* target_distance, int32_t* idx, uint8_t* flag);
 
 #ifdef __cplusplus
 }

@@ -113,6 +113,49 @@ class Oracle:
             raise ValueError("oracle: bad closed-loop arguments")
         return dict(pose=pose, act=act, u0=u0, target=tgt, idx=idx, iters_total=itot, iters_max=imax)
 
+    # ---- look-up table, crossing clamp, PID branch (oracle/pid_oracle.c) ------------------------------------------
+    def lookup(self, vx, vy, x):
+        vx = np.ascontiguousarray(vx, dtype=np.float32); vy = np.ascontiguousarray(vy, dtype=np.float32)
+        f = self.lib.orc_lookup
+        f.restype = C.c_float
+        f.argtypes = [_fp, _fp, C.c_int, C.c_float]
+        return np.array([f(_f(vx), _f(vy), len(vx), float(v)) for v in np.asarray(x, dtype=np.float32)], dtype=np.float32)
+
+    def crossing(self, px, py, vel, point_velocity, state, gains=(1.0, 0.0, 0.0, 0.01), cfg=(1.0, 0.35, 1.0, 0.05),
+                 npoints=None, layout="pb"):
+        """src/trajectory_point_follower.cpp:445-473 for a batch; `state` = (integral, prev, first) arrays, updated in
+        place like `point_velocity`."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, vel)]
+        B = point_velocity.shape[0]
+        if layout == "shared":
+            P, si, sp = arrs[0].shape[0], 0, 1
+        elif layout == "pb":
+            P, si, sp = arrs[0].shape[0], 1, B
+        else:
+            P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
+        npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+        c = (C.c_float * 4)(*cfg)
+        f = self.lib.orc_crossing_batch
+        f.restype = None
+        f.argtypes = [C.c_long, C.c_int, C.POINTER(C.c_int32), _fp, _fp, _fp, C.c_long, C.c_long, C.c_void_p] + \
+            [C.c_float] * 4 + [_fp, _fp, C.POINTER(C.c_uint8), _fp]
+        f(B, P, None if npts is None else npts.ctypes.data_as(C.POINTER(C.c_int32)), *[_f(a) for a in arrs], si, sp,
+          C.cast(c, C.c_void_p), *[float(g) for g in gains], _f(state[0]), _f(state[1]),
+          state[2].ctypes.data_as(C.POINTER(C.c_uint8)), _f(point_velocity))
+
+    def pid_branch(self, pos_x, pos_y, dir_x, dir_y, gains_front, gains_rear, state_front, state_rear):
+        B = pos_x.shape[0]
+        sf = np.zeros(B); sr = np.zeros(B); td = np.zeros(B, dtype=np.float32)
+        gf = (C.c_float * 4)(*gains_front); gr = (C.c_float * 4)(*gains_rear)
+        u8 = C.POINTER(C.c_uint8)
+        f = self.lib.orc_pid_branch_batch
+        f.restype = None
+        f.argtypes = [C.c_long] + [_fp] * 4 + [C.c_void_p, C.c_void_p, _fp, _fp, u8, _fp, _fp, u8, _dp, _dp, _fp]
+        f(B, _f(pos_x), _f(pos_y), _f(dir_x), _f(dir_y), C.cast(gf, C.c_void_p), C.cast(gr, C.c_void_p),
+          _f(state_front[0]), _f(state_front[1]), state_front[2].ctypes.data_as(u8),
+          _f(state_rear[0]), _f(state_rear[1]), state_rear[2].ctypes.data_as(u8), _d(sf), _d(sr), _f(td))
+        return sf, sr, td
+
     # ---- point extraction ---------------------------------------------------------------------------------
     def extract(self, px, py, dx, dy, vel, dist, npoints=None, layout="shared"):
         """layout 'shared': component arrays [P]; 'pb': [P][B] (point-major); 'bp': [B][P]."""

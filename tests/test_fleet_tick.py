@@ -28,8 +28,11 @@ def _fleet(B, P, seed):
     return f(x), f(y), f(np.cos(ang)), f(np.sin(ang)), f(vel), speed, dist
 
 
-def _restatement(oracle, px, py, dx, dy, vel, speed, dist, v_model, N):
+def _restatement(oracle, px, py, dx, dy, vel, speed, dist, v_model, N, pid_state=None):
     idx, flag, (ox, oy, odx, ody, ov) = oracle.extract(px, py, dx, dy, vel, dist, layout="pb")
+    if pid_state is None:                                # fresh slowDownCar per vehicle
+        B0 = len(speed); pid_state = (np.zeros(B0, np.float32), np.zeros(B0, np.float32), np.ones(B0, np.uint8))
+    oracle.crossing(px, py, vel, ov, pid_state)          # :445-473, the reference's config defaults
     v = speed.astype(np.float64); v = np.where(np.abs(v) < 0.1, 0.1, v)
     phi = np.arctan2(ody.astype(np.float64), odx.astype(np.float64)); ys = oy.astype(np.float64)
     if v_model is not None:
@@ -110,3 +113,127 @@ def test_fleet_tick_ragged_and_empty_polylines(oracle):
     assert np.all(got["target"][empty] == 0) and np.all(got["iters"][empty] == 0)      # already converged: 0 iterations
     assert np.array_equal(got["target_distance"][empty].view(np.uint32), dist[empty].view(np.uint32))   # |(d, 0)| = d
     assert np.array_equal(got["target"][:, 0].view(np.uint64), oy.astype(np.float64).view(np.uint64))
+
+
+def _stop_fleet(B, P, seed):
+    """Polylines with 0, 1 or several stop points (velocity == 0) at random indices, ahead of and behind the car."""
+    px, py, dx, dy, vel, speed, dist = _fleet(B, P, seed)
+    rng = np.random.default_rng(seed + 1)
+    vel[:] = 1.0
+    nstop = rng.integers(0, 4, B)
+    for b in range(B):
+        vel[rng.integers(0, P, nstop[b]), b] = 0.0
+    px = (px - np.float32(0.8) * rng.random(B).astype(np.float32)[None, :]).astype(np.float32)   # some points behind the car
+    return px, py, dx, dy, vel, speed, dist, nstop
+
+
+def test_crossing_clamp_and_pid_state_over_ticks(oracle):
+    """(f)3: the stop-at-crossing clamp (src/...:445-473) with one slowDownCar PID per vehicle resident on the device.
+    Non-trivial gains make the state matter: three ticks on moving polylines, ragged point counts, then reset()."""
+    from trajectory_controller_b200.engine import PID_SLOWDOWN, BatchedMPC, CrossingConfig
+    B, P, N = 3000, 40, 4
+    gains = (0.8, 0.5, 0.02, 0.01); cfgv = (0.9, 0.3, 1.2, 0.07)
+    px, py, dx, dy, vel, speed, dist, nstop = _stop_fleet(B, P, 33)
+    npts = np.random.default_rng(4).integers(0, P + 1, B).astype(np.int32); npts[::3] = P
+    st = (np.zeros(B, np.float32), np.zeros(B, np.float32), np.ones(B, np.uint8))
+    with BatchedMPC(2, 2, N, B) as eng:
+        eng.set_pid(PID_SLOWDOWN, *gains)
+        eng.set_crossing(CrossingConfig(*cfgv))
+        seen = set()
+        for tick in range(4):
+            if tick == 3:                                 # PID::reset() for the whole fleet
+                eng.reset_pid(PID_SLOWDOWN)
+                st = (np.zeros(B, np.float32), np.zeros(B, np.float32), np.ones(B, np.uint8))
+            pxt = (px - np.float32(0.12 * tick)).astype(np.float32)      # the car approaches the stop points
+            got = eng.fleet_tick_tobi(speed, dist, pxt, py, dx, dy, vel, layout="pb", npoints=npts)
+            idx, flag, (ox, oy, odx, ody, ov) = oracle.extract(pxt, py, dx, dy, vel, dist, npoints=npts, layout="pb")
+            raw = ov.copy()
+            oracle.crossing(pxt, py, vel, ov, st, gains=gains, cfg=cfgv, npoints=npts)
+            assert np.array_equal(got["target_speed"].view(np.uint32), ov.view(np.uint32)), tick
+            gi, gp, gf = eng.get_pid(PID_SLOWDOWN, B)
+            assert np.array_equal(gi.view(np.uint32), st[0].view(np.uint32)) and np.array_equal(gp.view(np.uint32), st[1].view(np.uint32))
+            assert np.array_equal(gf, st[2]), tick
+            assert np.array_equal(got["state"], (ov != 0).astype(np.uint8))
+            cross = ov < np.float32(0.5)
+            assert np.all(got["steering_front"][cross] == 0) and np.all(got["steering_rear"][cross] == 0)
+            seen |= {"clamped" if (ov != raw).any() else "", "zero" if ((ov == 0) & (raw != 0)).any() else "",
+                     "partial" if ((ov > 0) & (ov < np.float32(cfgv[0])) & (ov != raw)).any() else ""}
+        assert {"clamped", "zero", "partial"} <= seen
+        eng.set_crossing(None)                            # clamp off: the polyline's own velocity comes back
+        got = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb", npoints=npts)
+        _, _, (_, _, _, _, ov) = oracle.extract(px, py, dx, dy, vel, dist, npoints=npts, layout="pb")
+        assert np.array_equal(got["target_speed"].view(np.uint32), ov.view(np.uint32))
+
+
+def test_lookup_tables_on_device(oracle):
+    """LookupTable::linearSearch (src/...:66, :323) evaluated on the device: equals the restatement bit for bit, and a
+    tick with dist=None / device velocity table equals the tick fed with the host-evaluated values."""
+    from trajectory_controller_b200.engine import LOOKUP_DISTANCE, LOOKUP_VELOCITY, BatchedMPC, BmpcError
+    B, P, N = 2000, 48, 4
+    px, py, dx, dy, vel, speed, _ = _fleet(B, P, 17)
+    dvx, dvy = [0.0, 0.5, 1.0, 2.0, 3.0], [0.45, 0.5, 0.62, 0.9, 1.3]
+    vvx, vvy = [0.1, 1.0, 2.5], [0.3, 1.0, 2.0]
+    with BatchedMPC(2, 2, N, B) as eng:
+        with pytest.raises(BmpcError):
+            eng.fleet_tick_tobi(speed, None, px, py, dx, dy, vel, layout="pb")      # no table, no FOH
+        with pytest.raises(BmpcError):
+            eng.set_lookup(LOOKUP_DISTANCE, [0.0, 0.0], [1.0, 2.0])                # not ascending
+        eng.set_lookup(LOOKUP_DISTANCE, dvx, dvy)
+        xs = np.concatenate([speed, np.float32([-1, 0, 0.5, 3, 7, 1.0])])
+        assert np.array_equal(eng.lookup(LOOKUP_DISTANCE, xs).view(np.uint32), oracle.lookup(dvx, dvy, xs).view(np.uint32))
+        dist = oracle.lookup(dvx, dvy, speed)
+        a = eng.fleet_tick_tobi(speed, None, px, py, dx, dy, vel, layout="pb")
+        b = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb")
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+        # FOH drive mode, src/...:70-73 in float
+        eng.set_drive_mode(True, 0.6, 0.1)
+        a = eng.fleet_tick_tobi(speed, None, px, py, dx, dy, vel, layout="pb")
+        b = eng.fleet_tick_tobi(speed, (np.float32(0.6) + speed * np.float32(0.1)).astype(np.float32), px, py, dx, dy, vel, layout="pb")
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+        eng.set_drive_mode(False)
+        # velocity table: v (after the |v| < 0.1 rule, a double) -> float -> table -> double  (:323)
+        eng.set_lookup(LOOKUP_VELOCITY, vvx, vvy)
+        v = speed.astype(np.float64); v = np.where(np.abs(v) < 0.1, 0.1, v)
+        vm = oracle.lookup(vvx, vvy, v.astype(np.float32)).astype(np.float64)
+        a = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb")
+        b = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb", v_model=vm)
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+        eng.set_lookup(LOOKUP_VELOCITY, [], [])
+        c = eng.fleet_tick_tobi(speed, dist, px, py, dx, dy, vel, layout="pb")
+        assert not np.array_equal(c["steering_front"], a["steering_front"])
+
+
+def test_fleet_tick_pid_branch(oracle):
+    """The non-MPC branch (src/...:214-225): steering = pidFront(position.y), pidRear(directory.angle()), with the
+    per-vehicle PID states resident across ticks.  steering_front is exact; steering_rear goes through atan2f (CUDA's,
+    <= 2 ulp against libm): exact wherever the angle agrees, otherwise within the PID gain times the angle difference."""
+    from trajectory_controller_b200.engine import PID_FRONT, PID_REAR, BatchedMPC
+    B, P = 2500, 40
+    px, py, dx, dy, vel, speed, dist, _ = _stop_fleet(B, P, 51)
+    gf, gr = (1.2, 0.7, 0.03, 0.01), (0.9, 1.1, 0.01, 0.01)
+    sf_st = (np.zeros(B, np.float32), np.zeros(B, np.float32), np.ones(B, np.uint8))
+    sr_st = (np.zeros(B, np.float32), np.zeros(B, np.float32), np.ones(B, np.uint8))
+    sd_st = (np.zeros(B, np.float32), np.zeros(B, np.float32), np.ones(B, np.uint8))
+    with BatchedMPC(4, 1, 10, B) as eng:                  # any handle: no MPC shape involved
+        eng.set_pid(PID_FRONT, *gf); eng.set_pid(PID_REAR, *gr)
+        for tick in range(3):
+            pyt = (py + np.float32(0.01 * tick)).astype(np.float32)
+            got = eng.fleet_tick_pid(speed, dist, px, pyt, dx, dy, vel, layout="pb")
+            idx, flag, (ox, oy, odx, ody, ov) = oracle.extract(px, pyt, dx, dy, vel, dist, layout="pb")
+            oracle.crossing(px, pyt, vel, ov, sd_st)
+            sf, sr, td = oracle.pid_branch(ox, oy, odx, ody, gf, gr, sf_st, sr_st)
+            cross = ov < np.float32(0.5)
+            sf = np.where(cross, 0.0, sf); sr = np.where(cross, 0.0, sr)
+            assert np.array_equal(got["idx"], idx) and np.array_equal(got["flag"], flag)
+            assert np.array_equal(got["target_speed"].view(np.uint32), ov.view(np.uint32))
+            assert np.array_equal(got["target_distance"].view(np.uint32), td.view(np.uint32))
+            assert np.array_equal(got["steering_front"], sf), tick
+            assert np.max(np.abs(got["steering_rear"] - sr)) <= 1e-4, np.max(np.abs(got["steering_rear"] - sr))
+            assert (got["steering_rear"] == sr).mean() > 0.5
+            gi, gp, gfst = eng.get_pid(PID_FRONT, B)
+            assert np.array_equal(gi.view(np.uint32), sf_st[0].view(np.uint32)) and np.array_equal(gp.view(np.uint32), sf_st[1].view(np.uint32))
+            ri, rp, _ = eng.get_pid(PID_REAR, B)          # carry the device's rear state into the restatement so that an
+            sr_st[0][:] = ri; sr_st[1][:] = rp            # atan2f ulp does not accumulate through the integral term

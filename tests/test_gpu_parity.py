@@ -117,6 +117,129 @@ def test_random_models_vs_oracle(oracle, shape):
             assert np.array_equal(st, (ito >= mi).astype(np.uint8))
 
 
+@pytest.mark.parametrize("shape", [(2, 2, 4), (2, 1, 30), (4, 2, 10), (4, 1, 30)])
+def test_random_models_symmetric_bounds_vs_oracle(oracle, shape):
+    """Dense random models with lower == -upper: stage B runs its symmetric-bound kernel (pg_kernel.cuh, SYM), whose
+    compares are reformulated (carried on-a-bound mask, one |x| < h test per clamp, integer-pipe compares).  Same bar
+    as everywhere: value-exact controls, identical iteration counts — per-instance models, then one shared model."""
+    S, I, N = shape
+    rng = np.random.default_rng(500 + S * 7 + I * 3 + N)
+    B = 400
+    hi = rng.uniform(0.05, 1, (B, I))
+    pm = dict(A=np.eye(S) + 0.25 * rng.standard_normal((B, S, S)), B=rng.standard_normal((B, S, I)),
+              C=0.05 * rng.standard_normal((B, S)), Q=rng.uniform(0, 10, (B, S)) * (rng.random((B, S)) > 0.25),
+              R=rng.uniform(0.01, 2, (B, I)), lower=-hi, upper=hi)
+    x0 = rng.standard_normal((B, S)); tgt = rng.standard_normal((B, S))
+    for eps, mi in ((0.01, 10000), (1e-5, 400), (0.01, 51)):
+        uo, co, ito, _ = oracle.batch_cold(pm, N, x0, target=tgt, eps=eps, max_iter=mi, per_instance=True, nthreads=4)
+        assert (ito > 50).sum() > B // 10, "too few instances reach the projected-gradient phase"
+        for split in (1, 3):
+            with BatchedMPC(S, I, N, B) as eng:
+                eng.set_split(split)
+                eng.set_model(pm, per_instance=True)
+                eng.set_target(tgt)
+                eng.set_options(eps, mi)
+                u0, it, st = eng.solve(x0, keep_controls=True)
+                assert same_values(u0, uo) and same_values(eng.get_controls(B), co), (shape, eps, mi, split)
+                assert np.array_equal(it, ito) and np.array_equal(st, (ito >= mi).astype(np.uint8)), (shape, eps, mi, split)
+    one = {k: v[7] for k, v in pm.items()}
+    uo, co, ito, _ = oracle.batch_cold(one, N, x0, target=tgt, nthreads=4)
+    with BatchedMPC(S, I, N, B) as eng:
+        eng.set_model(one)
+        eng.set_target(tgt)
+        u0, it, _ = eng.solve(x0, keep_controls=True)
+        assert same_values(u0, uo) and same_values(eng.get_controls(B), co) and np.array_equal(it, ito)
+
+
+@pytest.mark.parametrize("split", [1, 0, 2, 3])
+def test_cold_solves_leave_persistent_state_alone(oracle, split):
+    """include/bmpc.h: a cold solve persists nothing.  warm -> cold (no KEEP_CONTROLS) -> warm on ONE handle must equal
+    a controller object that only saw the two warm calls — in every bmpc_set_split setting (the two-stage solve used to
+    park stage-A state in the persistent controls / v; it now parks in the hand-over ring's own slots)."""
+    m, N, B = W.bicycle4_model(), 30, 96
+    x0 = W.random_offsets_x0(B, 21)
+    ocs = [oracle.controller(m, N) for _ in range(B)]
+    with BatchedMPC(4, 1, N, B) as eng:
+        eng.set_split(split)
+        eng.set_model(m)
+        u0, it, _ = eng.solve(x0, warm=True)
+        uo = np.stack([ocs[b].step(x0[b]) for b in range(B)])
+        assert same_values(u0, uo) and np.array_equal(it, [o.iters for o in ocs])
+        assert (it > 50).mean() > 0.9
+        ctr, = (eng.get_controls(B),)
+        eng.solve(W.random_offsets_x0(B, 22))                       # cold, other inputs, nothing kept
+        eng.solve(-x0[:40])                                         # cold and ragged
+        assert np.array_equal(eng.get_controls(B).view(np.uint64), ctr.view(np.uint64))
+        x1 = x0 @ m.A.T + u0 @ m.B.T
+        u1, it1, _ = eng.solve(x1, warm=True)
+        uo1 = np.stack([ocs[b].step(x1[b]) for b in range(B)])
+        assert same_values(u1, uo1) and np.array_equal(it1, [o.iters for o in ocs])
+        assert same_values(eng.get_controls(B), np.stack([o.controls() for o in ocs]))
+
+
+def test_ragged_warm_solve_with_step_targets(oracle):
+    """A BMPC_WARM solve of count < capacity on a handle with per-step targets: the controllers that were not solved are
+    untouched dlib::mpc objects (mpc.h:236-237 runs only inside operator()), although the target ring's head is shared."""
+    m, N, B, cnt = W.bicycle4_model(1.2, 12, 4, 0.02), 10, 40, 23
+    rng = np.random.default_rng(9)
+    ocs = [oracle.controller(m, N) for _ in range(B)]
+    x = 0.3 * rng.standard_normal((B, 4))
+    with BatchedMPC(4, 1, N, B) as eng:
+        eng.set_model(m)
+        for t in range(N):
+            val = 0.1 * rng.standard_normal((B, 4))
+            eng.set_target(val, t)
+            for b in range(B):
+                ocs[b].set_target(val[b], t)
+        for k in range(5):
+            n = cnt if k % 2 == 0 else B                              # ragged, full, ragged, ...
+            u0, it, _ = eng.solve(x[:n], warm=True)
+            uo = np.stack([ocs[b].step(x[b]) for b in range(n)])
+            assert same_values(u0, uo) and np.array_equal(it, [ocs[b].iters for b in range(n)]), k
+            for b in (0, cnt - 1, cnt, B - 1):
+                for tt in (0, 3, N - 1):
+                    assert same_values(eng.get_target(tt, instance=b), ocs[b].targets()[tt]), (k, b, tt)
+            x[:n] = x[:n] @ m.A.T + u0 @ m.B.T
+
+
+def test_nonfinite_inputs_are_flagged(oracle):
+    """status bit BMPC_ST_NONFINITE: a NaN / inf in x0 or the targets (the reference logs isnan() of its outputs,
+    src/trajectory_point_follower.cpp:100-103).  Neighbours are unaffected.  The flagged solves are NOT claimed to
+    reproduce dlib's NaN propagation: dlib multiplies structural zeros out (0 * NaN = NaN, also inside diagm(Q) * x),
+    the kernels skip those products — hence the flag; their controls still lie inside the box."""
+    from trajectory_controller_b200.engine import ST_NONFINITE
+    m, N, B = W.bicycle4_model(), 30, 256
+    x0 = W.random_offsets_x0(B, 5)
+    x0[3, 0] = np.nan; x0[77, 1] = np.inf; x0[200, 2] = -np.inf; x0[201, 3] = np.nan
+    bad = np.zeros(B, dtype=bool); bad[[3, 77, 200, 201]] = True
+    uo, _, ito, _ = oracle.batch_cold(m, N, x0, nthreads=4, want_controls=False)
+    for split, special in ((1, True), (0, True), (3, True), (1, False), (0, False)):
+        with BatchedMPC(4, 1, N, B) as eng:
+            eng.set_split(split)
+            eng.set_specialization(special)
+            eng.set_model(m)
+            u0, it, st = eng.solve(x0)
+            assert np.all((st[bad] & ST_NONFINITE) != 0) and np.all((st[~bad] & ST_NONFINITE) == 0)
+            assert same_values(u0[~bad], uo[~bad]) and np.array_equal(it[~bad], ito[~bad]), split
+            assert np.all(np.abs(u0[bad]) <= W.ALPHA_MAX)          # whatever came out is inside the box and not a NaN
+
+
+def test_model_validation():
+    """dlib's requires clause (mpc.h:92-94) is enforced at the boundary instead of being undefined behaviour."""
+    from trajectory_controller_b200.engine import BmpcError
+    import copy
+    good = W.bicycle4_model()
+    with BatchedMPC(4, 1, 10, 4) as eng:
+        for field, val in (("R", np.array([0.0])), ("Q", np.array([1.0, -1.0, 0, 0])), ("upper", np.array([-1.0])),
+                           ("A", np.full((4, 4), np.nan)), ("lower", np.array([-np.inf]))):
+            bad = copy.deepcopy(good); setattr(bad, field, val)
+            with pytest.raises(BmpcError):
+                eng.set_model(bad)
+        eng.set_model(good)
+        u0, it, st = eng.solve(np.zeros((4, 4)))
+        assert np.all(u0 == 0) and np.all(it == 0)
+
+
 @pytest.mark.parametrize("which", ["bike10", "kat"])
 def test_persistent_controllers_vs_oracle(oracle, which):
     """Warm batch: per-instance states, per-step targets set at random times, shift semantics (mpc.h:229-237) and the
@@ -262,7 +385,7 @@ def test_split_solve_equals_one_kernel(shape):
         ms = [W.bicycle4_model(v=float(v)) for v in speeds]
         model = {k: np.stack([getattr(mm, k) for mm in ms]) for k in ("A", "B", "C", "Q", "R", "lower", "upper")}
     res = []
-    for split in (1, 0, 2):
+    for split in (1, 0, 2, 3):
         with BatchedMPC(S, I, N, B) as eng:
             eng.set_split(split)
             eng.set_model(model, per_instance=pim)
@@ -345,7 +468,7 @@ def test_time_slicing_is_invisible():
     for B in (65536, 100000):
         x0 = W.random_offsets_x0(B, 7)
         res = []
-        for split in (1, 2, 0):
+        for split in (1, 2, 0, 3):
             with BatchedMPC(4, 1, N, B) as eng:
                 eng.set_split(split)
                 eng.set_model(bike)

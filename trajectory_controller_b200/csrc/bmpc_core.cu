@@ -1,4 +1,5 @@
 // libbmpc.so — C ABI part 1: errors, lifetime, model, options.  See include/bmpc.h for the contract.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -100,6 +101,58 @@ const ShapeOps* select_pattern(int S, int I, int N, const double* A, const doubl
     return best;
 }
 
+// dlib::mpc's constructor contract — min(Q) >= 0, min(R) > 0, min(upper - lower) >= 0 (mpc.h:92-94) — and finite
+// entries, checked for every instance (dlib leaves a violation undefined; the engine rejects it).  *sym_ok reports
+// whether stage B's symmetric-bound kernel (pg_kernel.cuh, SYM) applies: lower == -upper with upper > 0, and a model
+// tame enough that no horizon recursion can overflow (the kernel's integer-pipe compares assume non-NaN values).
+static const char* validate_model(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
+                                  const double* R, const double* lo, const double* hi, long long count, bool as_float,
+                                  bool* sym_ok)
+{
+    bool sym = true;
+    double worst = 0;   // log10 of the growth bound, max over instances
+    auto val = [&](const double* v, long long i) { return as_float ? (double)(float)v[i] : v[i]; };
+    for (long long b = 0; b < count; ++b) {
+        double arow = 0, acol[16] = {0}, bmax = 0, qmax = 0, rmax = 0, hmax = 0;
+        for (int r = 0; r < S; ++r) {
+            double row = 0;
+            for (int k = 0; k < S; ++k) {
+                const double x = val(A, b * S * S + r * S + k);
+                if (!std::isfinite(x)) return "A has a non-finite entry";
+                row += std::fabs(x); if (k < 16) acol[k] += std::fabs(x);
+            }
+            arow = std::max(arow, row);
+        }
+        double anorm = std::max(1.0, arow);
+        for (int k = 0; k < S && k < 16; ++k) anorm = std::max(anorm, acol[k]);
+        for (int e = 0; e < S * I; ++e) {
+            const double x = val(B, b * S * I + e);
+            if (!std::isfinite(x)) return "B has a non-finite entry";
+            bmax = std::max(bmax, std::fabs(x));
+        }
+        for (int e = 0; e < S; ++e) {
+            const double c = val(C, b * S + e), q = val(Q, b * S + e);
+            if (!std::isfinite(c)) return "C has a non-finite entry";
+            if (!(q >= 0) || !std::isfinite(q)) return "Q must be finite and >= 0 (mpc.h:92 requires min(Q) >= 0)";
+            qmax = std::max(qmax, q);
+        }
+        for (int e = 0; e < I; ++e) {
+            const double r = val(R, b * I + e), l = val(lo, b * I + e), u = val(hi, b * I + e);
+            if (!(r > 0) || !std::isfinite(r)) return "R must be finite and > 0 (mpc.h:93 requires min(R) > 0)";
+            if (!std::isfinite(l) || !std::isfinite(u)) return "control bounds must be finite";
+            if (!(u >= l)) return "upper must be >= lower (mpc.h:94 requires min(upper-lower) >= 0)";
+            if (!(u > 0 && l == -u)) sym = false;
+            rmax = std::max(rmax, r); hmax = std::max(hmax, std::max(std::fabs(l), std::fabs(u)));
+        }
+        // |M| <= N g^N |B| I h, |Q M| and the adjoint chain add another N g^N |Q|, the gradient |B| S on top (mpc.h:275-283)
+        const double lg = 2.0 * N * std::log10(anorm) + 2.0 * std::log10((double)N) + 2.0 * std::log10(bmax * I + 1.0) +
+                          std::log10(qmax + 1.0) + std::log10(rmax + 1.0) + std::log10(hmax + 1.0) + std::log10((double)S);
+        worst = std::max(worst, lg);
+    }
+    *sym_ok = sym && worst < (as_float ? 30.0 : 250.0);
+    return nullptr;
+}
+
 }  // namespace bmpc
 
 using namespace bmpc;
@@ -107,7 +160,10 @@ using namespace bmpc;
 extern "C" {
 
 const char* bmpc_last_error(void) { return g_last_error.c_str(); }
-const char* bmpc_version(void) { return "bmpc 0.1 sm_100a (batched dlib::mpc-compatible linear MPC, CUDA)"; }
+#ifndef BMPC_BUILD_ID
+#define BMPC_BUILD_ID "unknown"
+#endif
+const char* bmpc_version(void) { return "bmpc 0.2 sm_100a build " BMPC_BUILD_ID " (batched dlib::mpc-compatible linear MPC, CUDA)"; }
 int bmpc_shape_supported(int S, int I, int N) { return find_shape(S, I, N) != nullptr; }
 
 int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precision, int mode, int device)
@@ -156,9 +212,16 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(h->vstate.alloc_zero(c * h->NI * es, h->stream), "alloc v");
     chk(h->target_const.alloc_zero(c * S * es, h->stream), "alloc target");
     chk(h->queue.alloc_zero(64, h->stream), "alloc queue");
-    chk(h->mmstate.alloc_zero(c * h->NI * es, h->stream), "alloc mmstate");
-    h->pg_ring = 1; while (h->pg_ring < c + 65536) h->pg_ring <<= 1;   // > capacity + lanes in flight (tickets)
+    // Hand-over ring: every instance can be parked at once, plus one open ticket per lane in flight (a launch of
+    // `count` instances keeps fewer than count + 32 * (grid + 1) lanes busy, bmpc_solve_resident_async).
+    {
+        const size_t lanes_max = (size_t)h->sm_count * 8 * 32, lanes_small = 2 * (c + 32);
+        const size_t want = c + (lanes_small < lanes_max ? lanes_small : lanes_max);
+        h->pg_ring = 64; while (h->pg_ring < want) h->pg_ring <<= 1;
+    }
     chk(h->pg_list.alloc_zero(h->pg_ring * 4, h->stream), "alloc pg_list");
+    chk(h->park.reserve(h->pg_ring * 3 * h->NI * es), "alloc park");
+    chk(h->park_iter.reserve(h->pg_ring * 4), "alloc park_iter");
     chk(h->small.alloc_zero(8 * 4096, h->stream), "alloc small");
     h->pinned_bytes = 8 * 4096;
     chk(cudaHostAlloc(&h->pinned, h->pinned_bytes, cudaHostAllocDefault), "cudaHostAlloc");
@@ -175,9 +238,11 @@ void bmpc_destroy(bmpc_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
                       &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
-                      &h->mmstate, &h->pg_list, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
+                      &h->pg_list, &h->park, &h->park_iter, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : h->ex) b.release();
+    for (DevBuf& b : h->lut) b.release();
+    for (DevBuf& b : h->pid_state) b.release();
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -206,7 +271,13 @@ int bmpc_set_split(bmpc_t* h, int enable)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_set_split: null handle");
     h->split = enable != 0;
-    h->slice = enable != 2;
+    if (enable >= 8) {   // developer A/B: 8 | 1 (fairness slices) | 2 (retirement of surplus warps) | 4 (symmetric-bound kernel)
+        h->slice = (enable & 1) != 0; h->retire = (enable & 2) != 0; h->sym = (enable & 4) != 0;
+    } else {
+        h->slice = enable != 2;
+        h->retire = enable != 2;
+        h->sym = enable != 3;
+    }
     return BMPC_OK;
 }
 const char* bmpc_pattern_name(bmpc_t* h) { return h && h->solve_ops ? h->solve_ops->pattern : ""; }
@@ -250,6 +321,10 @@ int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C,
     BMPC_CUDA(cudaSetDevice(h->device));
     const long long cnt = per_instance ? count : 1;
     if (cnt < 1 || cnt > h->cap) return fail(BMPC_E_INVALID, "bmpc_set_model: count out of range");
+    {   // dlib's requires clause (mpc.h:92-94, mpc_abstract.h:90-97) plus finiteness, for every instance
+        const char* bad = validate_model(S, I, N, A, B, C, Q, R, lower, upper, cnt, h->elem == 4, &h->sym_ok);
+        if (bad) return fail(BMPC_E_INVALID, std::string("bmpc_set_model: ") + bad);
+    }
     int rc;
     if ((rc = upload_soa(h, A, cnt, S * S, h->mA)) || (rc = upload_soa(h, B, cnt, S * I, h->mB)) ||
         (rc = upload_soa(h, C, cnt, S, h->mC)) || (rc = upload_soa(h, Q, cnt, S, h->mQ)) ||

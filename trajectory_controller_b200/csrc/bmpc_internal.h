@@ -37,6 +37,10 @@ cudaError_t aos_to_soa(const double* d_aos, void* d_soa, long long count, int le
                        cudaStream_t st);
 cudaError_t soa_to_aos(const void* d_soa, double* d_aos, long long count, int len, long long stride, int elem_size,
                        cudaStream_t st);
+// Ragged warm solve with per-step targets: keeps the logical targets of the instances [first, first+count) in place
+// while the shared ring head advances by one (see k_rotate_targets).
+cudaError_t rotate_targets(void* d_target, long long first, long long count, int S, int N, long long stride, int elem_size,
+                           cudaStream_t st);
 // Broadcast one host vector of `len` doubles (passed by value through a small device buffer) into [len][stride].
 cudaError_t broadcast_rows(const double* d_vec, void* d_soa, long long count, int len, long long stride, int elem_size,
                            cudaStream_t st);
@@ -79,9 +83,13 @@ struct bmpc_handle {
 
     // state
     bmpc::DevBuf x0, u0, iters, status, controls, vstate, target_const, target_full, queue;
-    bmpc::DevBuf mmstate, pg_list;   // split solve: stage A -> stage B hand-over (pg_kernel.cuh)
-    size_t pg_ring = 0;              // ring capacity (power of two >= cap)
+    bmpc::DevBuf pg_list, park, park_iter;   // split solve: hand-over ring and the by-slot state of parked instances (pg_kernel.cuh)
+    bool ring_dirty = true;          // pg_list may hold entries of an earlier launch (bmpc_solve_resident_async)
+    size_t pg_ring = 0;              // ring capacity (a power of two >= capacity + lanes in flight)
+    bool sym_ok = false;             // the model meets the preconditions of stage B's symmetric-bound kernel (bmpc_set_model)
     bool slice = true;               // stage B may time-slice small batches
+    bool retire = true;              // stage B may retire surplus warps near the end of a launch (bmpc_set_split(h, 2) turns it off)
+    bool sym = true;                 // stage B may use its symmetric-bound kernel (bmpc_set_split(h, 3) turns it off)
     bool split = true;               // bmpc_set_split; the two-stage solve is used whenever the shape offers it
     bool full_targets = false;
     int head = 0;
@@ -92,6 +100,17 @@ struct bmpc_handle {
     void* pinned = nullptr;       // host pinned mirror for small transfers
     size_t pinned_bytes = 0;
     bmpc::DevBuf ex[16];          // trajectory-point extraction buffers
+
+    // fleet tick (fleet_tick.cu): look-up tables, crossing clamp, per-vehicle PID controllers
+    bmpc::DevBuf lut[2];          // 2n floats: vx | vy   (BMPC_LOOKUP_DISTANCE, BMPC_LOOKUP_VELOCITY)
+    int lut_n[2] = {0, 0};
+    bool foh = false;             // drive mode FOH: look-ahead = foh_min + v * foh_slope (src/...:70-73)
+    float foh_min = 0.6f, foh_slope = 0.1f;
+    bool crossing_on = true;      // the reference always applies the clamp (src/...:445-473)
+    bmpc_crossing_config crossing{1.0f, 0.35f, 1.0f, 0.05f};
+    float pid_gain[3][4] = {{1, 0, 0, 0.01f}, {1, 1, 0, 0.01f}, {1, 1, 0, 0.01f}};   // src/...:296-298 defaults
+    bmpc::DevBuf pid_state[3];    // float integral[cap] | float prev[cap] | uint8 first[cap]
+    bool pid_ready[3] = {false, false, false};
 
     // closed loop (closed_loop.cu)
     bool cl_ready = false;

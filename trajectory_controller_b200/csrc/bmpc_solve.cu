@@ -150,7 +150,7 @@ int bmpc_copy_state(bmpc_t* dst, bmpc_t* src)
     return BMPC_OK;
 }
 
-int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
+static int upload_x0_async(bmpc_t* h, int64_t count, const double* x0)
 {
     if (!h || !x0) return fail(BMPC_E_INVALID, "bmpc_upload_x0: null argument");
     if (count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_upload_x0: count out of capacity");
@@ -160,6 +160,14 @@ int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
     BMPC_CUDA(cudaMemcpyAsync(h->stage.p, x0, bytes, cudaMemcpyHostToDevice, h->stream));
     BMPC_CUDA(aos_to_soa((const double*)h->stage.p, h->x0.p, count, h->S, h->cap, h->elem, h->stream));
     h->launches++;
+    return BMPC_OK;
+}
+
+int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
+{
+    int rc = upload_x0_async(h, count, x0);
+    if (rc) return rc;
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));   // synchronous on return (bmpc.h): x0 may be reused by the caller
     return BMPC_OK;
 }
 
@@ -187,12 +195,29 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     // Two-stage solve (pg_kernel.cuh): needs the stage-B kernel for this shape, iterations beyond the 50 coordinate
     // steps, and eps > 0 (stage B tests "|df| >= eps" instead of carrying max_df; bmpc_set_options enforces eps > 0).
     const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0;
-    g.split = split; g.mmstate = h->mmstate.p; g.pg_list = (uint32_t*)h->pg_list.p;
+    g.split = split; g.pg_list = (uint32_t*)h->pg_list.p;
+    g.sym = 0;
+    if (split && h->sym_ok && h->sym) {   // the symmetric-bound stage-B kernel, where the shape has one (register-resident horizons)
+        KernelInfo kp0;
+        BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, 0, &kp0));
+        g.sym = kp0.sym_ok;
+    }
     g.pg_mask = (unsigned)(h->pg_ring - 1);
-    // time slicing pays when lanes get only a few instances each (pg_kernel.cuh); 8 warps x 32 lanes per SM are resident
-    // (measured, scripts/slice_threshold.py: +4..10 % between 1 and 4 instances per lane, -4 % below, neutral above)
-    g.pg_slice = h->slice && count > 1ll * h->sm_count * 256 && count <= 4ll * h->sm_count * 256;
-    if (split) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
+    g.park = h->park.p; g.park_iter = (uint32_t*)h->park_iter.p;
+    // Stage-B scheduling (pg_kernel.cuh).  Slot reuse (parking) is what retirement and fairness slices need; it costs a
+    // fence per resumed instance, so very large batches, whose tail is a small share of the launch, run without it.
+    // Fairness slices pay when lanes get only a few instances each (measured, scripts/slice_threshold.py: +4..10 %
+    // between 1 and 4 instances per lane, -4 % below, neutral above); 8 warps x 32 lanes per SM are resident.
+    const long long lanes = 1ll * h->sm_count * 256;
+    const bool small_enough = count <= 8 * lanes;
+    g.pg_slice = h->slice && small_enough && count > lanes && count <= 4 * lanes;
+    // retirement needs more than one warp per SM sub-partition's worth of instances to have anything to retire
+    const bool retire = h->retire && small_enough && count > 1ll * h->sm_count * 128;
+    g.pg_reuse = (g.pg_slice || retire) ? (1 | (retire ? 2 : 0)) : 0;   // bit 0: parking, bit 1: retirement
+    // A launch that recycles ring slots needs every slot empty at the start and leaves it so; one that does not leaves
+    // stage A's entries behind.  So the ring is wiped only when a recycling launch follows a non-recycling one.
+    if (split && g.pg_reuse && h->ring_dirty) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
+    if (split) h->ring_dirty = !g.pg_reuse;
     BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;
@@ -213,14 +238,22 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     if (split) {
         BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
         KernelInfo kp;
-        BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &kp));
+        BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, g.sym, &kp));
         g.warp_limit_b = limit_for(kp.warps);
         BMPC_CUDA(h->solve_ops->pg(h->precision, h->mode, h->per_instance, g, grid, h->stream));
         h->launches++;
     }
     BMPC_CUDA(cudaEventRecord(h->ev1, h->stream));
     h->timed = true;
-    if (warm && h->full_targets) h->head = h->head + 1 == h->N ? 0 : h->head + 1;   // mpc.h:236-237
+    if (warm && h->full_targets) {                                                  // mpc.h:236-237
+        h->head = h->head + 1 == h->N ? 0 : h->head + 1;
+        // the head is shared by all slots of the handle, but only the first `count` controllers ran operator():
+        // the others keep their logical targets (their rows follow the head)
+        if (count < h->cap) {
+            BMPC_CUDA(rotate_targets(h->target_full.p, count, h->cap - count, h->S, h->N, h->cap, h->elem, h->stream));
+            h->launches++;
+        }
+    }
     return BMPC_OK;
 }
 
@@ -237,14 +270,18 @@ int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t
     BMPC_CUDA(cudaMemcpyAsync(u0, d_out, bytes, cudaMemcpyDeviceToHost, h->stream));
     if (iters) BMPC_CUDA(cudaMemcpyAsync(iters, h->iters.p, (size_t)count * 4, cudaMemcpyDeviceToHost, h->stream));
     if (status) BMPC_CUDA(cudaMemcpyAsync(status, h->status.p, (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    unsigned long long* err = (unsigned long long*)h->pinned;
+    BMPC_CUDA(cudaMemcpyAsync(err, (char*)h->queue.p + 32, 8, cudaMemcpyDeviceToHost, h->stream));
     BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    if (*err) h->ring_dirty = true;
+    if (*err) return fail(BMPC_E_STATE, "bmpc_download: the last solve gave up (hand-over ring overrun); results are incomplete");
     return BMPC_OK;
 }
 
 int bmpc_solve(bmpc_t* h, int64_t count, const double* x0, double* u0, uint32_t* iters, uint8_t* status, unsigned flags)
 {
     int rc;
-    if ((rc = bmpc_upload_x0(h, count, x0))) return rc;
+    if ((rc = upload_x0_async(h, count, x0))) return rc;   // x0 stays valid: bmpc_download synchronises before returning
     if ((rc = bmpc_solve_resident_async(h, count, flags))) return rc;
     return bmpc_download(h, count, u0, iters, status);
 }
@@ -254,6 +291,15 @@ int bmpc_sync(bmpc_t* h)
     if (!h) return fail(BMPC_E_INVALID, "bmpc_sync: null handle");
     BMPC_CUDA(cudaSetDevice(h->device));
     BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_device_results(bmpc_t* h, void** u0, void** iters, void** status)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_device_results: null handle");
+    if (u0) *u0 = h->u0.p;
+    if (iters) *iters = h->iters.p;
+    if (status) *status = h->status.p;
     return BMPC_OK;
 }
 
@@ -289,7 +335,7 @@ int bmpc_pg_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* 
     if (!h->solve_ops->has_pg) return fail(BMPC_E_UNSUPPORTED, "bmpc_pg_kernel_info: this shape has no stage-B kernel (one-kernel solve)");
     BMPC_CUDA(cudaSetDevice(h->device));
     KernelInfo ki;
-    BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, &ki));
+    BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, h->sym_ok && h->sym, &ki));
     if (grid) *grid = h->sm_count;
     if (block) *block = ki.block;
     if (smem_bytes) *smem_bytes = ki.smem_bytes;

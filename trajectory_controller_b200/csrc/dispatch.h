@@ -20,7 +20,10 @@ struct GenericSolve {
     const void *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
     unsigned long long* queue;                   // 64 bytes: [0] stage-A claims, [1] stage-B list length, [2] stage-B claims
     int split;                                   // run the two-stage solve (pg_kernel.cuh)
-    void* mmstate; uint32_t* pg_list; unsigned pg_mask; int pg_slice;
+    uint32_t* pg_list; unsigned pg_mask; int pg_slice;
+    void* park; uint32_t* park_iter;             // by-ring-slot state of parked instances (pg_kernel.cuh)
+    int pg_reuse;                                // stage B recycles ring slots (parking enabled)
+    int sym;                                     // bounds are symmetric and the model is tame: stage B may run its SYM kernel
     int warp_limit_a, warp_limit_b;              // warps per CTA that take work in stage A / stage B
 };
 
@@ -31,7 +34,7 @@ struct GenericCtor {
     void* mlambda; void* mqdiag;
 };
 
-struct KernelInfo { int block, smem_bytes, regs, warps, local_bytes; };
+struct KernelInfo { int block, smem_bytes, regs, warps, local_bytes, sym_ok; };
 
 // One (shape, structural pattern) instantiation family.  `ctor` is only provided by the dense pattern.
 struct ShapeOps {
@@ -44,7 +47,7 @@ struct ShapeOps {
     // stage B of the split solve; has_pg == 0 when the shape keeps u[]/MM[] out of registers (long horizons)
     int has_pg;
     cudaError_t (*pg)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
-    cudaError_t (*pg_info)(int precision, int mode, int pim, KernelInfo* out);
+    cudaError_t (*pg_info)(int precision, int mode, int pim, int sym, KernelInfo* out);
 };
 
 }  // namespace bmpc

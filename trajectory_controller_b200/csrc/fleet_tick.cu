@@ -1,14 +1,18 @@
-// libbmpc.so — one tobiMPC control tick of TrajectoryPointController::cycle() for a FLEET of vehicles, resident on the
-// device.  Per vehicle, /root/reference/src/trajectory_point_follower.cpp:
-//   :66-76    look-ahead distance (evaluated by the caller) -> getTrajectoryPoint (k_extract, :392-443)
+// libbmpc.so — one control tick of TrajectoryPointController::cycle() for a FLEET of vehicles, resident on the device
+// (SURVEY.md §8(f) ranks 1 and 3).  Per vehicle, /root/reference/src/trajectory_point_follower.cpp:
+//   :66-76    look-ahead distance (caller-side, or LookupTable / FOH formula on the device: k_lookahead)
+//             -> getTrajectoryPoint (k_extract, :392-443) -> the "stop at crossing" clamp (k_crossing, :445-473)
+//   tobiMPC branch (bmpc_fleet_tick_tobi):
 //   :77-85    |v| < 0.1 -> v = 0.1;  phi_soll = atan2(dir.y, dir.x);  y_soll = position.y
-//   :301-389  mpcControllerTobi: A = [1 Tv; 0 1], B = [0 Tv; Tv/l -Tv/l], C = 0, Q = (w_y, w_phi), R = (w_sf, w_sr),
-//             bounds -+22 deg (:16-18), a FRESH dlib::mpc<2,2,4> (constructor math on the device, ctor_kernel.cuh),
-//             set_target((y_soll, phi_soll)), operator()((0,0))      -> cold batched solve
+//   :301-389  mpcControllerTobi: v = lookup(v) (:323), A = [1 Tv; 0 1], B = [0 Tv; Tv/l -Tv/l], C = 0, Q = (w_y, w_phi),
+//             R = (w_sf, w_sr), bounds -+22 deg (:16-18), a FRESH dlib::mpc<2,2,4> (constructor math on the device,
+//             ctor_kernel.cuh), set_target((y_soll, phi_soll)), operator()((0,0))      -> cold batched solve
 //   :114-125  CarCommand fields;  :276-283 targetSpeed < 0.5 -> both steering angles 0
-// Kernels: k_extract -> k_tick_prepare -> ctor_kernel -> solve (stage A / stage B) -> k_tick_finish; nothing crosses
-// PCIe between them.  Every operation is a separately rounded IEEE operation; the one function that cannot be made
-// bit-identical to the reference's host is atan2 (CUDA's double atan2, <= 2 ulp, against glibc's): see bmpc.h.
+//   PID branch (bmpc_fleet_tick_pid): :214-225 steering = pid(position.y), pid(directory.angle())
+// Kernels: [k_lookahead] -> k_extract -> [k_crossing] -> k_tick_prepare -> ctor_kernel -> solve (stage A / stage B) ->
+// k_tick_finish; nothing crosses PCIe between them.  Every operation is a separately rounded IEEE operation; the
+// functions that cannot be made bit-identical to the reference's host are atan2 / atan2f (CUDA's, <= 2 ulp, against
+// glibc's): see bmpc.h.  PID / LookupTable semantics: include/bmpc.h (sensor_utils, lms_math are not vendored).
 #include <cmath>
 
 #include "bmpc_internal.h"
@@ -16,11 +20,109 @@
 namespace bmpc {
 namespace {
 
+// lms::math::LookupTable<float, ASC>::linearSearch (float, every operation rounded on its own)
+__device__ __forceinline__ float lut_eval(const float* __restrict__ t, int n, float x)
+{
+    if (n <= 0) return x;
+    const float* vx = t; const float* vy = t + n;
+    if (x <= vx[0]) return vy[0];
+    for (int i = 1; i < n; ++i)
+        if (x <= vx[i])
+            return __fadd_rn(vy[i - 1], __fdiv_rn(__fmul_rn(__fsub_rn(vy[i], vy[i - 1]), __fsub_rn(x, vx[i - 1])),
+                                                  __fsub_rn(vx[i], vx[i - 1])));
+    return vy[n - 1];
+}
+
+// :66 / :70-73 look-ahead distance per vehicle; also the plain table evaluation of bmpc_lookup (foh = 0)
+__global__ void k_lookahead(long long count, const float* __restrict__ x, const float* __restrict__ table, int n, int foh,
+                            float foh_min, float foh_slope, float* __restrict__ y)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    const float v = x[b];
+    y[b] = foh ? __fadd_rn(foh_min, __fmul_rn(v, foh_slope)) : lut_eval(table, n, v);
+}
+
+struct PidGains { float kp, ki, kd, dt; };
+// sensor_utils::PID::pid (float): state in registers, the caller stores it back
+__device__ __forceinline__ float pid_step(const PidGains& g, float& integral, float& prev, bool& first, float e)
+{
+    integral = __fadd_rn(integral, __fmul_rn(e, g.dt));
+    const float deriv = first ? 0.0f : __fdiv_rn(__fsub_rn(e, prev), g.dt);
+    prev = e; first = false;
+    return __fadd_rn(__fadd_rn(__fmul_rn(g.kp, e), __fmul_rn(g.ki, integral)), __fmul_rn(g.kd, deriv));
+}
+
+// :445-473, one thread per vehicle: a sequential scan (the PID is stateful along the polyline).  Reads the velocity
+// row of every point and the position only of stop points; with the point-major layout every load is coalesced.
+__global__ void k_crossing(long long count, int P, const int32_t* __restrict__ npoints, const float* __restrict__ px,
+                           const float* __restrict__ py, const float* __restrict__ vel, long long si, long long sp,
+                           bmpc_crossing_config cfg, PidGains g, float* __restrict__ integral, float* __restrict__ prev,
+                           uint8_t* __restrict__ first, float* __restrict__ point_velocity)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    int n = npoints ? npoints[b] : P;
+    if (n > P) n = P;
+    if (n <= 0) return;                                               // :404-407 returned before the clamp
+    const long long o = b * si;
+    float in = integral[b], pr = prev[b]; bool fi = first[b] != 0, touched = false;
+    float minVelocity = cfg.max_velocity_crossing;                    // :446
+    float pv = 0.0f; bool set = false;
+    for (int k = 0; k < n; ++k) {                                     // :447
+        if (vel[o + k * sp] != 0.0f) continue;                        // :448
+        const float x = px[o + k * sp], y = py[o + k * sp];
+        const float len = __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));
+        const float sg = (float)((0.0f < x) - (x < 0.0f));            // lms::math::sgn
+        const float dts = __fsub_rn(__fmul_rn(sg, len), cfg.stopping_distance);   // :449
+        touched = true;
+        if (dts < cfg.distance_to_stop) {                             // :450
+            float v = pid_step(g, in, pr, fi, dts);                   // :453
+            if (isnan(v) || v >= cfg.max_velocity_crossing) v = cfg.max_velocity_crossing;   // :454-456
+            if (dts <= cfg.crossing_safety_zone || v < 0.0f) v = 0.0f;                       // :457-459
+            if (v < minVelocity) minVelocity = v;                     // :460-462
+            pv = minVelocity; set = true;                             // :464
+            if (minVelocity == 0.0f) break;                           // :466-468
+        } else { in = 0.0f; pr = 0.0f; fi = true; }                   // :469-471 slowDownCar.reset()
+    }
+    if (touched) { integral[b] = in; prev[b] = pr; first[b] = fi ? 1 : 0; }
+    if (set) point_velocity[b] = pv;
+}
+
+// :214-225 + :276-283, one thread per vehicle
+__global__ void k_pid_branch(long long count, const float* __restrict__ opx, const float* __restrict__ opy,
+                             const float* __restrict__ odx, const float* __restrict__ ody, const float* __restrict__ ovel,
+                             PidGains gf, PidGains gr, float* __restrict__ fi_, float* __restrict__ fp_, uint8_t* __restrict__ ff_,
+                             float* __restrict__ ri_, float* __restrict__ rp_, uint8_t* __restrict__ rf_,
+                             double* __restrict__ sf, double* __restrict__ sr, float* __restrict__ tspeed, float* __restrict__ tdist)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    float in = fi_[b], pr = fp_[b]; bool fi = ff_[b] != 0;
+    double f = (double)pid_step(gf, in, pr, fi, opy[b]);                          // :219
+    fi_[b] = in; fp_[b] = pr; ff_[b] = 0;
+    in = ri_[b]; pr = rp_[b]; fi = rf_[b] != 0;
+    double r = (double)pid_step(gr, in, pr, fi, atan2f(ody[b], odx[b]));          // :220 directory.angle()
+    ri_[b] = in; rp_[b] = pr; rf_[b] = 0;
+    const float x = opx[b], y = opy[b], sp = ovel[b];
+    tdist[b] = __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));           // :224 position.length()
+    if (sp < 0.5f) { f = 0.0; r = 0.0; }                                          // :276-283
+    sf[b] = f; sr[b] = r; tspeed[b] = sp;                                         // :221-223
+}
+
+__global__ void k_pid_fill(long long count, float* __restrict__ integral, float* __restrict__ prev, uint8_t* __restrict__ first)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    integral[b] = 0.0f; prev[b] = 0.0f; first[b] = 1;
+}
+
 struct TickParams {
     long long count, stride;
     double T, l, w_y, w_phi, w_sf, w_sr, alpha_max;
     const float* velocity;      // [count] car->velocity()
-    const double* v_model;      // [count] result of m_mpcLookupVelocity.linearSearch(v) (:323), or null = v itself
+    const double* v_model;      // [count] result of m_mpcLookupVelocity.linearSearch(v) (:323) from the caller, or null
+    const float* vtable; int vn;   // ... then the BMPC_LOOKUP_VELOCITY table on the device (vn = 0: v itself)
     const float *opx, *opy, *odx, *ody;   // extracted trajectory point
 };
 
@@ -37,6 +139,7 @@ __global__ void k_tick_prepare(TickParams q, T* __restrict__ mA, T* __restrict__
     const double phi_soll = atan2((double)q.ody[b], (double)q.odx[b]); // :84 (float components widened first)
     const double y_soll = (double)q.opy[b];                             // :85
     if (q.v_model) v = q.v_model[b];                                    // :323
+    else if (q.vn > 0) v = (double)lut_eval(q.vtable, q.vn, (float)v);  // LookupTable<float>: double -> float -> double
     const double Tv = __dmul_rn(q.T, v);                                // T*v
     const double Tvl = __ddiv_rn(Tv, q.l);                              // T*v/l
     mA[0 * s + b] = T(1); mA[1 * s + b] = T(Tv); mA[2 * s + b] = T(0); mA[3 * s + b] = T(1);       // :326-327
@@ -75,49 +178,225 @@ const ShapeOps* find_pattern(int S, int I, int N, const char* name);   // bmpc_c
 
 using namespace bmpc;
 
-extern "C" int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_config* cfg, const float* velocity,
-                                    const double* v_model, const float* dist, int P, const int32_t* npoints,
-                                    const float* px, const float* py, const float* dx, const float* dy, const float* vel,
-                                    int64_t stride_instance, int64_t stride_point, double* steering_front,
-                                    double* steering_rear, float* target_speed, float* target_distance, uint8_t* state,
-                                    int32_t* idx, uint8_t* flag, double* target, uint32_t* iters)
+namespace {
+
+inline unsigned grid_for(long long count, int block) { return (unsigned)((count + block - 1) / block); }
+
+int pid_state_ready(bmpc_t* h, int which)
 {
-    if (!h || !cfg || !velocity || !dist || !steering_front || !steering_rear || !target_speed || !target_distance || !state)
-        return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: null argument");
-    if (h->S != 2 || h->I != 2) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: the handle must be a (2,2,N) controller (mpcControllerTobi, src/...:303-366)");
-    if (count < 1 || count > h->cap || P < 0) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: count / P out of range");
-    if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: null trajectory array");
-    if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: negative stride");
+    if (h->pid_ready[which]) return BMPC_OK;
+    const size_t cap = (size_t)h->cap;
+    BMPC_CUDA(h->pid_state[which].reserve(cap * 9));
+    float* in = (float*)h->pid_state[which].p;
+    k_pid_fill<<<grid_for(h->cap, 256), 256, 0, h->stream>>>(h->cap, in, in + cap, (uint8_t*)(in + 2 * cap));
+    BMPC_CUDA(cudaGetLastError());
+    h->launches++;
+    h->pid_ready[which] = true;
+    return BMPC_OK;
+}
+inline PidGains gains_of(const bmpc_t* h, int which) { return PidGains{h->pid_gain[which][0], h->pid_gain[which][1], h->pid_gain[which][2], h->pid_gain[which][3]}; }
+
+// The front end both branches share: uploads, look-ahead, getTrajectoryPoint, crossing clamp.  Device results:
+// ex[7] idx, ex[8] flag, ex[9..13] the trajectory point (x, y, dir x, dir y, velocity), ex[14] car velocity (float).
+int fleet_front(bmpc_t* h, const char* who, int64_t count, const float* velocity, const float* dist, int P,
+                const int32_t* npoints, const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                int64_t stride_instance, int64_t stride_point)
+{
+    if (count < 1 || count > h->cap || P < 0) return fail(BMPC_E_INVALID, std::string(who) + ": count / P out of range");
+    if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, std::string(who) + ": null trajectory array");
+    if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, std::string(who) + ": negative stride");
+    if (!dist && !h->foh && h->lut_n[BMPC_LOOKUP_DISTANCE] <= 0)
+        return fail(BMPC_E_STATE, std::string(who) + ": dist == NULL needs the BMPC_LOOKUP_DISTANCE table (bmpc_set_lookup) or FOH drive mode");
     BMPC_CUDA(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
-    const size_t c = (size_t)count, es = (size_t)h->elem, cap = (size_t)h->cap;
-
-    // ---- trajectory point (same buffers and kernel as bmpc_extract_points, results stay on the device) -------------
+    const size_t c = (size_t)count;
     const size_t nflt = P > 0 ? (size_t)((count - 1) * stride_instance + (int64_t)(P - 1) * stride_point + 1) : 0;
     const float* src[5] = {px, py, dx, dy, vel};
     for (int a = 0; a < 5; ++a) {
         BMPC_CUDA(h->ex[a].reserve(nflt * 4 + 4));
         if (nflt) BMPC_CUDA(cudaMemcpyAsync(h->ex[a].p, src[a], nflt * 4, cudaMemcpyHostToDevice, st));
     }
+    const size_t voff = ((c * 4 + 7) / 8) * 8;
+    BMPC_CUDA(h->ex[14].reserve(voff + c * 8));                           // velocity (float) | v_model (double)
+    BMPC_CUDA(cudaMemcpyAsync(h->ex[14].p, velocity, c * 4, cudaMemcpyHostToDevice, st));
     BMPC_CUDA(h->ex[5].reserve(c * 4));
-    BMPC_CUDA(cudaMemcpyAsync(h->ex[5].p, dist, c * 4, cudaMemcpyHostToDevice, st));
+    if (dist) BMPC_CUDA(cudaMemcpyAsync(h->ex[5].p, dist, c * 4, cudaMemcpyHostToDevice, st));
+    else {                                                                // :66 / :70-73 on the device
+        k_lookahead<<<grid_for(count, 256), 256, 0, st>>>(count, (const float*)h->ex[14].p, (const float*)h->lut[BMPC_LOOKUP_DISTANCE].p,
+                                                          h->lut_n[BMPC_LOOKUP_DISTANCE], h->foh ? 1 : 0, h->foh_min, h->foh_slope, (float*)h->ex[5].p);
+        BMPC_CUDA(cudaGetLastError());
+        h->launches++;
+    }
     if (npoints) {
         BMPC_CUDA(h->ex[6].reserve(c * 4));
         BMPC_CUDA(cudaMemcpyAsync(h->ex[6].p, npoints, c * 4, cudaMemcpyHostToDevice, st));
     }
     for (int a = 7; a < 14; ++a) BMPC_CUDA(h->ex[a].reserve(c * 4));
-    BMPC_CUDA(launch_extract(count, P, npoints ? (const int32_t*)h->ex[6].p : nullptr, (const float*)h->ex[0].p,
-                             (const float*)h->ex[1].p, (const float*)h->ex[2].p, (const float*)h->ex[3].p,
-                             (const float*)h->ex[4].p, stride_instance, stride_point, (const float*)h->ex[5].p,
-                             (int32_t*)h->ex[7].p, (uint8_t*)h->ex[8].p, (float*)h->ex[9].p, (float*)h->ex[10].p,
-                             (float*)h->ex[11].p, (float*)h->ex[12].p, (float*)h->ex[13].p, st));
+    const int32_t* d_np = npoints ? (const int32_t*)h->ex[6].p : nullptr;
+    BMPC_CUDA(launch_extract(count, P, d_np, (const float*)h->ex[0].p, (const float*)h->ex[1].p, (const float*)h->ex[2].p,
+                             (const float*)h->ex[3].p, (const float*)h->ex[4].p, stride_instance, stride_point,
+                             (const float*)h->ex[5].p, (int32_t*)h->ex[7].p, (uint8_t*)h->ex[8].p, (float*)h->ex[9].p,
+                             (float*)h->ex[10].p, (float*)h->ex[11].p, (float*)h->ex[12].p, (float*)h->ex[13].p, st));
     h->launches++;
+    if (h->crossing_on && P > 0) {                                        // :445-473
+        int rc = pid_state_ready(h, BMPC_PID_SLOWDOWN);
+        if (rc) return rc;
+        float* in = (float*)h->pid_state[BMPC_PID_SLOWDOWN].p;
+        const size_t cap = (size_t)h->cap;
+        k_crossing<<<grid_for(count, 128), 128, 0, st>>>(count, P, d_np, (const float*)h->ex[0].p, (const float*)h->ex[1].p,
+                                                         (const float*)h->ex[4].p, stride_instance, stride_point, h->crossing,
+                                                         gains_of(h, BMPC_PID_SLOWDOWN), in, in + cap, (uint8_t*)(in + 2 * cap),
+                                                         (float*)h->ex[13].p);
+        BMPC_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    return BMPC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bmpc_set_lookup(bmpc_t* h, int which, int n, const float* vx, const float* vy)
+{
+    if (!h || which < 0 || which > 1 || n < 0 || n > 4096 || (n > 0 && (!vx || !vy)))
+        return fail(BMPC_E_INVALID, "bmpc_set_lookup: bad argument (which in {0,1}, 0 <= n <= 4096)");
+    for (int i = 1; i < n; ++i)
+        if (!(vx[i] > vx[i - 1])) return fail(BMPC_E_INVALID, "bmpc_set_lookup: vx must be strictly ascending (LookupTableOrder::ASC)");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    if (n > 0) {
+        BMPC_CUDA(h->lut[which].reserve((size_t)n * 8));
+        BMPC_CUDA(cudaMemcpyAsync(h->lut[which].p, vx, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+        BMPC_CUDA(cudaMemcpyAsync((float*)h->lut[which].p + n, vy, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->lut_n[which] = n;
+    return BMPC_OK;
+}
+
+int bmpc_lookup(bmpc_t* h, int which, int64_t count, const float* x, float* y)
+{
+    if (!h || which < 0 || which > 1 || !x || !y || count < 1) return fail(BMPC_E_INVALID, "bmpc_lookup: bad argument");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    BMPC_CUDA(h->stage.reserve((size_t)count * 8));
+    float* d = (float*)h->stage.p;
+    BMPC_CUDA(cudaMemcpyAsync(d, x, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    k_lookahead<<<grid_for(count, 256), 256, 0, h->stream>>>(count, d, (const float*)h->lut[which].p, h->lut_n[which], 0, 0.f, 0.f, d + count);
+    BMPC_CUDA(cudaGetLastError());
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(y, d + count, (size_t)count * 4, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_fleet_set_drive_mode(bmpc_t* h, int foh, float regelpunkt_min, float regelpunkt_slope)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_fleet_set_drive_mode: null handle");
+    h->foh = foh != 0; h->foh_min = regelpunkt_min; h->foh_slope = regelpunkt_slope;
+    return BMPC_OK;
+}
+
+int bmpc_fleet_set_crossing(bmpc_t* h, const bmpc_crossing_config* cfg)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_fleet_set_crossing: null handle");
+    h->crossing_on = cfg != nullptr;
+    if (cfg) h->crossing = *cfg;
+    return BMPC_OK;
+}
+
+int bmpc_fleet_set_pid(bmpc_t* h, int which, float kp, float ki, float kd, float dt)
+{
+    if (!h || which < 0 || which > 2) return fail(BMPC_E_INVALID, "bmpc_fleet_set_pid: bad argument");
+    h->pid_gain[which][0] = kp; h->pid_gain[which][1] = ki; h->pid_gain[which][2] = kd; h->pid_gain[which][3] = dt;
+    return BMPC_OK;
+}
+
+int bmpc_fleet_reset_pid(bmpc_t* h, int which)
+{
+    if (!h || which < 0 || which > 2) return fail(BMPC_E_INVALID, "bmpc_fleet_reset_pid: bad argument");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    h->pid_ready[which] = false;
+    return pid_state_ready(h, which);
+}
+
+int bmpc_fleet_get_pid(bmpc_t* h, int which, int64_t count, float* integral, float* prev, uint8_t* first)
+{
+    if (!h || which < 0 || which > 2 || count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_fleet_get_pid: bad argument");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    int rc = pid_state_ready(h, which);
+    if (rc) return rc;
+    const float* in = (const float*)h->pid_state[which].p; const size_t cap = (size_t)h->cap, c = (size_t)count;
+    if (integral) BMPC_CUDA(cudaMemcpyAsync(integral, in, c * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (prev) BMPC_CUDA(cudaMemcpyAsync(prev, in + cap, c * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (first) BMPC_CUDA(cudaMemcpyAsync(first, in + 2 * cap, c, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_fleet_put_pid(bmpc_t* h, int which, int64_t count, const float* integral, const float* prev, const uint8_t* first)
+{
+    if (!h || which < 0 || which > 2 || count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_fleet_put_pid: bad argument");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    int rc = pid_state_ready(h, which);
+    if (rc) return rc;
+    float* in = (float*)h->pid_state[which].p; const size_t cap = (size_t)h->cap, c = (size_t)count;
+    if (integral) BMPC_CUDA(cudaMemcpyAsync(in, integral, c * 4, cudaMemcpyHostToDevice, h->stream));
+    if (prev) BMPC_CUDA(cudaMemcpyAsync(in + cap, prev, c * 4, cudaMemcpyHostToDevice, h->stream));
+    if (first) BMPC_CUDA(cudaMemcpyAsync(in + 2 * cap, first, c, cudaMemcpyHostToDevice, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
+int bmpc_fleet_tick_pid(bmpc_t* h, int64_t count, const float* velocity, const float* dist, int P, const int32_t* npoints,
+                        const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                        int64_t stride_instance, int64_t stride_point, double* steering_front, double* steering_rear,
+                        float* target_speed, float* target_distance, int32_t* idx, uint8_t* flag)
+{
+    if (!h || !velocity || !steering_front || !steering_rear || !target_speed || !target_distance)
+        return fail(BMPC_E_INVALID, "bmpc_fleet_tick_pid: null argument");
+    int rc = fleet_front(h, "bmpc_fleet_tick_pid", count, velocity, dist, P, npoints, px, py, dx, dy, vel, stride_instance, stride_point);
+    if (rc) return rc;
+    if ((rc = pid_state_ready(h, BMPC_PID_FRONT)) || (rc = pid_state_ready(h, BMPC_PID_REAR))) return rc;
+    cudaStream_t st = h->stream;
+    const size_t c = (size_t)count, cap = (size_t)h->cap;
+    BMPC_CUDA(h->ex[15].reserve(c * (8 + 8 + 4 + 4)));
+    double* d_sf = (double*)h->ex[15].p; double* d_sr = d_sf + c;
+    float* d_ts = (float*)(d_sr + c); float* d_td = d_ts + c;
+    float* fs = (float*)h->pid_state[BMPC_PID_FRONT].p; float* rs = (float*)h->pid_state[BMPC_PID_REAR].p;
+    k_pid_branch<<<grid_for(count, 128), 128, 0, st>>>(count, (const float*)h->ex[9].p, (const float*)h->ex[10].p,
+                                                       (const float*)h->ex[11].p, (const float*)h->ex[12].p, (const float*)h->ex[13].p,
+                                                       gains_of(h, BMPC_PID_FRONT), gains_of(h, BMPC_PID_REAR), fs, fs + cap,
+                                                       (uint8_t*)(fs + 2 * cap), rs, rs + cap, (uint8_t*)(rs + 2 * cap), d_sf, d_sr, d_ts, d_td);
+    BMPC_CUDA(cudaGetLastError());
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(steering_front, d_sf, c * 8, cudaMemcpyDeviceToHost, st));
+    BMPC_CUDA(cudaMemcpyAsync(steering_rear, d_sr, c * 8, cudaMemcpyDeviceToHost, st));
+    BMPC_CUDA(cudaMemcpyAsync(target_speed, d_ts, c * 4, cudaMemcpyDeviceToHost, st));
+    BMPC_CUDA(cudaMemcpyAsync(target_distance, d_td, c * 4, cudaMemcpyDeviceToHost, st));
+    if (idx) BMPC_CUDA(cudaMemcpyAsync(idx, h->ex[7].p, c * 4, cudaMemcpyDeviceToHost, st));
+    if (flag) BMPC_CUDA(cudaMemcpyAsync(flag, h->ex[8].p, c, cudaMemcpyDeviceToHost, st));
+    BMPC_CUDA(cudaStreamSynchronize(st));
+    return BMPC_OK;
+}
+
+int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_config* cfg, const float* velocity,
+                         const double* v_model, const float* dist, int P, const int32_t* npoints,
+                         const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                         int64_t stride_instance, int64_t stride_point, double* steering_front,
+                         double* steering_rear, float* target_speed, float* target_distance, uint8_t* state,
+                         int32_t* idx, uint8_t* flag, double* target, uint32_t* iters)
+{
+    if (!h || !cfg || !velocity || !steering_front || !steering_rear || !target_speed || !target_distance || !state)
+        return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: null argument");
+    if (h->S != 2 || h->I != 2) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: the handle must be a (2,2,N) controller (mpcControllerTobi, src/...:303-366)");
+    int rc = fleet_front(h, "bmpc_fleet_tick_tobi", count, velocity, dist, P, npoints, px, py, dx, dy, vel, stride_instance, stride_point);
+    if (rc) return rc;
+    cudaStream_t st = h->stream;
+    const size_t c = (size_t)count, es = (size_t)h->elem, cap = (size_t)h->cap;
 
     // ---- per-vehicle model, target and zero state ---------------------------------------------------------------------
     const size_t voff = ((c * 4 + 7) / 8) * 8;
-    BMPC_CUDA(h->ex[14].reserve(voff + c * 8));                           // velocity (float) | v_model (double)
     BMPC_CUDA(h->ex[15].reserve(cap * 8 * 2 + c * (8 + 8 + 4 + 4 + 1)));   // tgt_dbg [2][cap] | outputs
-    BMPC_CUDA(cudaMemcpyAsync(h->ex[14].p, velocity, c * 4, cudaMemcpyHostToDevice, st));
     double* d_vmodel = nullptr;
     if (v_model) {
         d_vmodel = (double*)((char*)h->ex[14].p + voff);
@@ -132,6 +411,7 @@ extern "C" int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_co
     q.count = count; q.stride = h->cap; q.T = cfg->T; q.l = cfg->l; q.w_y = cfg->weight_y; q.w_phi = cfg->weight_phi;
     q.w_sf = cfg->weight_steering_front; q.w_sr = cfg->weight_steering_rear; q.alpha_max = cfg->alpha_max;
     q.velocity = (const float*)h->ex[14].p; q.v_model = d_vmodel;
+    q.vtable = (const float*)h->lut[BMPC_LOOKUP_VELOCITY].p; q.vn = h->lut_n[BMPC_LOOKUP_VELOCITY];
     q.opx = (const float*)h->ex[9].p; q.opy = (const float*)h->ex[10].p; q.odx = (const float*)h->ex[11].p; q.ody = (const float*)h->ex[12].p;
     double* tgt_dbg = (double*)h->ex[15].p;
     const unsigned grid = (unsigned)((count + 127) / 128);
@@ -154,7 +434,7 @@ extern "C" int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_co
     h->full_targets = false; h->head = 0;                         // set_target(val): one target for all horizon steps
     const ShapeOps* tobi = h->specialize ? find_pattern(h->S, h->I, h->N, "tobi") : nullptr;   // holds by construction
     h->solve_ops = tobi ? tobi : h->ops;
-    int rc = bmpc_solve_resident_async(h, count, 0);
+    rc = bmpc_solve_resident_async(h, count, 0);
     if (rc) return rc;
 
     // ---- CarCommand fields ----------------------------------------------------------------------------------------------
@@ -187,3 +467,5 @@ extern "C" int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_co
     BMPC_CUDA(cudaStreamSynchronize(st));
     return BMPC_OK;
 }
+
+}  // extern "C"

@@ -6,21 +6,68 @@
 namespace bmpc {
 namespace {
 
-// One thread per (instance, element).  Reads are strided by `len` doubles (len <= 16 in practice, every byte of
-// a fetched sector is used by a neighbouring thread of the same warp via L1), writes are coalesced.
+// Transposes between instance-major doubles [count][len] and [len][stride] of T, a tile of kTile instances per block
+// staged through shared memory (row pitch len | 1: conflict-free both ways), so that BOTH sides move whole 32-byte
+// sectors: the flat instance-major side is walked linearly, the element-major side row by row.  Pure HBM traffic:
+// (8 + sizeof T) * len bytes per instance.
+constexpr int kTile = 128;
 template <typename T>
 __global__ void k_aos_to_soa(const double* __restrict__ in, T* __restrict__ out, long long count, int len, long long stride)
+{
+    extern __shared__ double tile[];
+    const long long b0 = (long long)blockIdx.x * kTile;
+    const int nb = (int)((count - b0) < kTile ? (count - b0) : kTile), pitch = len | 1;
+    for (int f = threadIdx.x; f < nb * len; f += blockDim.x) tile[(f / len) * pitch + f % len] = in[b0 * len + f];
+    __syncthreads();
+    for (int f = threadIdx.x; f < nb * len; f += blockDim.x) {
+        const int e = f / nb, b = f % nb;
+        out[(long long)e * stride + b0 + b] = (T)tile[b * pitch + e];
+    }
+}
+template <typename T>
+__global__ void k_soa_to_aos(const T* __restrict__ in, double* __restrict__ out, long long count, int len, long long stride)
+{
+    extern __shared__ double tile[];
+    const long long b0 = (long long)blockIdx.x * kTile;
+    const int nb = (int)((count - b0) < kTile ? (count - b0) : kTile), pitch = len | 1;
+    for (int f = threadIdx.x; f < nb * len; f += blockDim.x) {
+        const int e = f / nb, b = f % nb;
+        tile[b * pitch + e] = (double)in[(long long)e * stride + b0 + b];
+    }
+    __syncthreads();
+    for (int f = threadIdx.x; f < nb * len; f += blockDim.x) out[b0 * len + f] = tile[(f / len) * pitch + f % len];
+}
+// Un-tiled forms for rows too long for a shared-memory tile (len > kTileMaxLen): one thread per instance.
+constexpr int kTileMaxLen = 40;
+template <typename T>
+__global__ void k_aos_to_soa_long(const double* __restrict__ in, T* __restrict__ out, long long count, int len, long long stride)
 {
     const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= count) return;
     for (int e = 0; e < len; ++e) out[(long long)e * stride + b] = (T)in[b * len + e];
 }
 template <typename T>
-__global__ void k_soa_to_aos(const T* __restrict__ in, double* __restrict__ out, long long count, int len, long long stride)
+__global__ void k_soa_to_aos_long(const T* __restrict__ in, double* __restrict__ out, long long count, int len, long long stride)
 {
     const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= count) return;
     for (int e = 0; e < len; ++e) out[b * len + e] = (double)in[(long long)e * stride + b];
+}
+// Undoes, for the instances a ragged warm solve did NOT touch, the advance of the shared target-ring head
+// (mpc.h:236-237 runs only inside operator()): their rows move one physical slot forward so that every logical
+// horizon step keeps its value under the new head.  One thread per (instance, state row).
+template <typename T>
+__global__ void k_rotate_targets(T* __restrict__ target, long long first, long long count, int S, int N, long long stride)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count * S) return;
+    const long long b = first + t / S;
+    const int r = (int)(t % S);
+    T carry = target[((long long)(N - 1) * S + r) * stride + b];
+    for (int ph = 0; ph < N; ++ph) {
+        T* cell = target + ((long long)ph * S + r) * stride + b;
+        const T keep = *cell; *cell = carry; carry = keep;
+    }
 }
 template <typename T>
 __global__ void k_broadcast(const double* __restrict__ vec, T* __restrict__ out, long long count, int len, long long stride)
@@ -86,16 +133,36 @@ cudaError_t aos_to_soa(const double* d_aos, void* d_soa, long long count, int le
                        cudaStream_t st)
 {
     if (count <= 0) return cudaSuccess;
-    if (elem_size == 8) k_aos_to_soa<double><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (double*)d_soa, count, len, stride);
-    else k_aos_to_soa<float><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (float*)d_soa, count, len, stride);
+    if (len > kTileMaxLen) {
+        if (elem_size == 8) k_aos_to_soa_long<double><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (double*)d_soa, count, len, stride);
+        else k_aos_to_soa_long<float><<<blocks_for(count, 256), 256, 0, st>>>(d_aos, (float*)d_soa, count, len, stride);
+        return cudaGetLastError();
+    }
+    const size_t sm = (size_t)kTile * (len | 1) * 8;
+    if (elem_size == 8) k_aos_to_soa<double><<<blocks_for(count, kTile), 256, sm, st>>>(d_aos, (double*)d_soa, count, len, stride);
+    else k_aos_to_soa<float><<<blocks_for(count, kTile), 256, sm, st>>>(d_aos, (float*)d_soa, count, len, stride);
     return cudaGetLastError();
 }
 cudaError_t soa_to_aos(const void* d_soa, double* d_aos, long long count, int len, long long stride, int elem_size,
                        cudaStream_t st)
 {
     if (count <= 0) return cudaSuccess;
-    if (elem_size == 8) k_soa_to_aos<double><<<blocks_for(count, 256), 256, 0, st>>>((const double*)d_soa, d_aos, count, len, stride);
-    else k_soa_to_aos<float><<<blocks_for(count, 256), 256, 0, st>>>((const float*)d_soa, d_aos, count, len, stride);
+    if (len > kTileMaxLen) {
+        if (elem_size == 8) k_soa_to_aos_long<double><<<blocks_for(count, 256), 256, 0, st>>>((const double*)d_soa, d_aos, count, len, stride);
+        else k_soa_to_aos_long<float><<<blocks_for(count, 256), 256, 0, st>>>((const float*)d_soa, d_aos, count, len, stride);
+        return cudaGetLastError();
+    }
+    const size_t sm = (size_t)kTile * (len | 1) * 8;
+    if (elem_size == 8) k_soa_to_aos<double><<<blocks_for(count, kTile), 256, sm, st>>>((const double*)d_soa, d_aos, count, len, stride);
+    else k_soa_to_aos<float><<<blocks_for(count, kTile), 256, sm, st>>>((const float*)d_soa, d_aos, count, len, stride);
+    return cudaGetLastError();
+}
+cudaError_t rotate_targets(void* d_target, long long first, long long count, int S, int N, long long stride, int elem_size,
+                           cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    if (elem_size == 8) k_rotate_targets<double><<<blocks_for(count * S, 256), 256, 0, st>>>((double*)d_target, first, count, S, N, stride);
+    else k_rotate_targets<float><<<blocks_for(count * S, 256), 256, 0, st>>>((float*)d_target, first, count, S, N, stride);
     return cudaGetLastError();
 }
 cudaError_t broadcast_rows(const double* d_vec, void* d_soa, long long count, int len, long long stride, int elem_size,

@@ -41,7 +41,8 @@ void fill_params(SolveParams<T, S_, I_, N_>& p, const GenericSolve& g)
     p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
     p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
     p.queue = g.queue;
-    p.split = g.split; p.mmstate = (T*)g.mmstate; p.pg_list = g.pg_list; p.pg_mask = g.pg_mask; p.pg_slice = g.pg_slice;
+    p.split = g.split; p.pg_list = g.pg_list; p.pg_mask = g.pg_mask; p.pg_slice = g.pg_slice;
+    p.park = (T*)g.park; p.park_iter = g.park_iter; p.pg_reuse = g.pg_reuse; p.sym = g.sym;
 }
 
 template <typename T, bool EXACT, bool PIM>
@@ -66,40 +67,53 @@ cudaError_t info_solve(KernelInfo* out)
     cudaError_t e = cudaFuncGetAttributes(&a, solve_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>);
     if (e != cudaSuccess) return e;
     out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
-    out->local_bytes = (int)a.localSizeBytes;
+    out->local_bytes = (int)a.localSizeBytes; out->sym_ok = 0;
     return cudaSuccess;
 }
 
 constexpr bool kHasPg = PgLayout<double, S_, I_, N_, false, PAT_>::OK && PgLayout<float, S_, I_, N_, false, PAT_>::OK;
+
+template <typename T, bool EXACT, bool PIM, bool SYM>
+cudaError_t launch_pg_t(const GenericSolve& g, int grid, cudaStream_t st)
+{
+    using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
+    SolveParams<T, S_, I_, N_> p;
+    fill_params<T, PIM>(p, g);
+    p.warp_limit = g.warp_limit_b;
+    auto kern = pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_, SYM>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
+    return cudaGetLastError();
+}
 
 template <typename T, bool EXACT, bool PIM>
 cudaError_t launch_pg(const GenericSolve& g, int grid, cudaStream_t st)
 {
     if constexpr (!kHasPg) return cudaErrorNotSupported;
     else {
-        using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
-        SolveParams<T, S_, I_, N_> p;
-        fill_params<T, PIM>(p, g);
-        p.warp_limit = g.warp_limit_b;
-        auto kern = pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>;
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
-        return cudaGetLastError();
+        if constexpr (PgLayout<T, S_, I_, N_, PIM, PAT_>::SYM_OK) {
+            if (g.sym) return launch_pg_t<T, EXACT, PIM, true>(g, grid, st);
+        }
+        return launch_pg_t<T, EXACT, PIM, false>(g, grid, st);
     }
 }
 
 template <typename T, bool EXACT, bool PIM>
-cudaError_t info_pg(KernelInfo* out)
+cudaError_t info_pg(int sym, KernelInfo* out)
 {
     if constexpr (!kHasPg) return cudaErrorNotSupported;
     else {
         using L = PgLayout<T, S_, I_, N_, PIM, PAT_>;
         cudaFuncAttributes a;
-        cudaError_t e = cudaFuncGetAttributes(&a, pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_>);
+        cudaError_t e;
+        if constexpr (L::SYM_OK) {
+            if (sym) e = cudaFuncGetAttributes(&a, pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_, true>);
+            else e = cudaFuncGetAttributes(&a, pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_, false>);
+        } else e = cudaFuncGetAttributes(&a, pg_kernel<T, S_, I_, N_, EXACT, PIM, PAT_, false>);
         if (e != cudaSuccess) return e;
         out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
-        out->local_bytes = (int)a.localSizeBytes;
+        out->local_bytes = (int)a.localSizeBytes; out->sym_ok = L::SYM_OK ? 1 : 0;
         return cudaSuccess;
     }
 }
@@ -133,8 +147,8 @@ cudaError_t info_entry(int precision, int mode, int pim, KernelInfo* out)
 { BMPC_DISPATCH(info_solve, out); }
 cudaError_t pg_entry(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st)
 { BMPC_DISPATCH(launch_pg, g, grid, st); }
-cudaError_t pg_info_entry(int precision, int mode, int pim, KernelInfo* out)
-{ BMPC_DISPATCH(info_pg, out); }
+cudaError_t pg_info_entry(int precision, int mode, int pim, int sym, KernelInfo* out)
+{ BMPC_DISPATCH(info_pg, sym, out); }
 template <bool DENSE>
 cudaError_t ctor_entry_t(int precision, int mode, const GenericCtor& g, cudaStream_t st)
 {

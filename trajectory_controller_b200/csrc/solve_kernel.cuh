@@ -64,14 +64,18 @@ struct SolveParams {
     uint8_t* status;     // [stride]
     // per-instance models, SoA [elem][stride]
     const T *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
-    unsigned long long* queue;   // [0] next unclaimed instance; [1] ring tail; [2] ring head; [3] instances stage B has not finished
-    // split solve (pg_kernel.cuh): stage A parks an instance that reaches iter == 50 and appends it to pg_list
+    unsigned long long* queue;   // [0] next unclaimed instance; [1] ring tail; [2] ring head; [3] instances stage B has
+                                 // not finished; [4] error word (ring overrun)
+    // split solve (pg_kernel.cuh): stage A parks an instance that reaches iter == 50 in a slot of the hand-over ring
     int split;
-    T* mmstate;          // [N*I][stride]  the linear term MM of mpc.h:266, handed from stage A to stage B
-    uint32_t* pg_list;   // ring of instance ids, capacity pg_mask + 1 (a power of two >= stride), 0xffffffff = empty
+    uint32_t* pg_list;   // ring of instance ids, capacity pg_mask + 1 (a power of two), 0xffffffff = empty
     unsigned pg_mask;
+    T* park;             // [3*N*I][pg_mask + 1]  state of parked instances BY RING SLOT: controls, v, linear term MM (mpc.h:266)
+    uint32_t* park_iter; // [pg_mask + 1]         their iteration counters
     int warp_limit;      // warps of a CTA that take work (small batches are spread one warp per SM sub-partition first)
     int pg_slice;        // stage B may time-slice small batches (pg_kernel.cuh)
+    int pg_reuse;        // stage B recycles ring slots (parking enabled)
+    int sym;             // stage B runs the symmetric-bound kernel: instances whose linear term is not finite stay in stage A
 };
 
 __host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n += int(x & 1u); x >>= 1; } return n; }
@@ -347,7 +351,7 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
     SV sv(p, sm);
 
     long long inst = -1;
-    bool need = true, active = false, setup = false;
+    bool need = true, active = false, setup = false, nonfinite = false;
     uint32_t iter = 0;
     bool v_dirty = false;
     T xs[S], tgc[S];
@@ -419,10 +423,21 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         else sv.template pass<false>(false, xs, tgc, 0, max_df, max_idx, max_val);
 
         // ---------------- per-lane state machine ---------------------------------------------------------------------
+        bool hand = false;
         if (active) {
             bool finished = false, hit_max = false;
             if (setup) {
                 setup = false; iter = 0;                                   // mpc.h:270
+                // a NaN / inf in x0, the targets or the model reaches every later number through the linear term
+                // (x0 and a constant target are looked at directly: a pattern-specialised kernel never reads the
+                // entries that only meet structural zeros)
+                bool finite = true;
+#pragma unroll(SV::UNROLL_K)
+                for (int k = 0; k < NI; ++k) finite &= (SV::to_bits(sv.getMM(k)) & SV::kInfBits) != SV::kInfBits;
+#pragma unroll
+                for (int r = 0; r < S; ++r)
+                    finite &= (SV::to_bits(xs[r]) & SV::kInfBits) != SV::kInfBits && (SV::to_bits(tgc[r]) & SV::kInfBits) != SV::kInfBits;
+                nonfinite = !finite;
                 if (p.max_iter == 0) { finished = true; hit_max = true; }  // loop body never runs (mpc.h:271)
             } else if (max_df < p.eps) {                                   // mpc.h:310-311
                 finished = true;
@@ -472,25 +487,17 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                 ++iter;
                 if (iter >= p.max_iter) { finished = true; hit_max = true; }   // mpc.h:271
                 else if (p.split && iter == 50) {
-                    // Hand over to stage B (pg_kernel.cuh): the projected-gradient phase continues there from
-                    // exactly this state — controls, v (set by mpc.h:331-334 one line above, or stale) and MM.
-#pragma unroll(SV::UNROLL_K)
-                    for (int k = 0; k < NI; ++k) {
-                        p.controls[(long long)k * p.stride + inst] = sv.getU(k);
-                        p.vstate[(long long)k * p.stride + inst] = sm[(L::O_V + k) * 32];
-                        p.mmstate[(long long)k * p.stride + inst] = sv.getMM(k);
-                    }
-                    p.iters[inst] = iter;                                  // stage B resumes from here
-                    p.pg_list[(unsigned)atomicAdd(p.queue + 1, 1ull) & p.pg_mask] = (uint32_t)inst;
-                    atomicAdd(p.queue + 3, 1ull);                          // instances stage B still has to finish
-                    active = false; need = true;
+                    // Hand over to stage B (pg_kernel.cuh).  Its symmetric-bound kernel assumes finite numbers; an
+                    // instance whose linear term is not (NaN / inf in x0 or the targets) finishes here instead, with
+                    // the literal arithmetic of the one-kernel path.
+                    hand = !(p.sym && nonfinite);
                 }
             }
             if (finished) {
 #pragma unroll
                 for (int j = 0; j < I; ++j) p.u0[(long long)j * p.stride + inst] = sv.getU(j);   // mpc.h:239
                 p.iters[inst] = iter;
-                p.status[inst] = hit_max ? 1 : 0;
+                p.status[inst] = (hit_max ? 1 : 0) | (nonfinite ? 2 : 0);
                 if (p.warm || p.keep_controls) {
 #pragma unroll(SV::UNROLL_K)
                     for (int k = 0; k < NI; ++k) p.controls[(long long)k * p.stride + inst] = sv.getU(k);
@@ -510,6 +517,33 @@ solve_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
                                 p.target[((long long)last * S + r) * p.stride + inst];
                     }
                 }
+                active = false; need = true;
+            }
+        }
+        // ---------------- hand-over to stage B: the projected-gradient phase continues there from exactly this state —
+        // controls, v (set by mpc.h:331-334, or stale) and MM.  The lanes of a warp reach iter == 50 together, so they
+        // take consecutive ring slots (one aggregated atomic) and the by-slot state rows are written coalesced.
+        const unsigned handmask = __ballot_sync(FULL, hand);
+        if (handmask) {
+            const int leader = __ffs(handmask) - 1;
+            unsigned long long pos = 0;
+            if (lane == leader) {
+                pos = atomicAdd(p.queue + 1, (unsigned long long)__popc(handmask));
+                atomicAdd(p.queue + 3, (unsigned long long)__popc(handmask));   // instances stage B still has to finish
+            }
+            pos = __shfl_sync(FULL, pos, leader);
+            if (hand) {
+                const unsigned ps = (unsigned)(pos + (unsigned long long)__popc(handmask & ((1u << lane) - 1u))) & p.pg_mask;
+                const long long rstride = (long long)p.pg_mask + 1;
+#pragma unroll(SV::UNROLL_K)
+                for (int k = 0; k < NI; ++k) {
+                    p.park[(long long)k * rstride + ps] = sv.getU(k);
+                    p.park[(long long)(NI + k) * rstride + ps] = sm[(L::O_V + k) * 32];
+                    p.park[(long long)(2 * NI + k) * rstride + ps] = sv.getMM(k);
+                }
+                p.park_iter[ps] = iter;                                // stage B resumes from here
+                p.status[inst] = nonfinite ? 2 : 0;                    // stage B adds BMPC_ST_MAXITER
+                p.pg_list[ps] = (uint32_t)inst;
                 active = false; need = true;
             }
         }

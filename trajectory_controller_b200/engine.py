@@ -23,6 +23,7 @@ FP64, FP32 = 64, 32
 EXACT, FAST = 0, 1
 WARM, KEEP_CONTROLS = 1, 2
 ST_MAXITER = 1
+ST_NONFINITE = 2
 PT_INTERPOLATED, PT_LAST, PT_EMPTY = 0, 1, 2
 
 _dp = C.POINTER(C.c_double)
@@ -56,6 +57,7 @@ SIGNATURES = {
     "bmpc_solve_resident_async": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint]),
     "bmpc_download": (C.c_int, [C.c_void_p, C.c_int64, _dp, _u32p, _u8p]),
     "bmpc_sync": (C.c_int, [C.c_void_p]),
+    "bmpc_device_results": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 3),
     "bmpc_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bmpc_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
     "bmpc_last_stage_ms": (C.c_int, [C.c_void_p, _fp, _fp]),
@@ -66,6 +68,16 @@ SIGNATURES = {
     "bmpc_extract_points": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
     "bmpc_fleet_tick_tobi": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, _fp, _dp, _fp, C.c_int, _i32p] + [_fp] * 5 +
                              [C.c_int64, C.c_int64, _dp, _dp, _fp, _fp, _u8p, _i32p, _u8p, _dp, _u32p]),
+    "bmpc_set_lookup": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _fp, _fp]),
+    "bmpc_lookup": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _fp, _fp]),
+    "bmpc_fleet_set_drive_mode": (C.c_int, [C.c_void_p, C.c_int, C.c_float, C.c_float]),
+    "bmpc_fleet_set_crossing": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bmpc_fleet_set_pid": (C.c_int, [C.c_void_p, C.c_int] + [C.c_float] * 4),
+    "bmpc_fleet_reset_pid": (C.c_int, [C.c_void_p, C.c_int]),
+    "bmpc_fleet_get_pid": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _fp, _fp, _u8p]),
+    "bmpc_fleet_put_pid": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _fp, _fp, _u8p]),
+    "bmpc_fleet_tick_pid": (C.c_int, [C.c_void_p, C.c_int64, _fp, _fp, C.c_int, _i32p] + [_fp] * 5 +
+                            [C.c_int64, C.c_int64, _dp, _dp, _fp, _fp, _i32p, _u8p]),
     "bmpc_cl_init": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p] + [_dp] * 6),
     "bmpc_cl_run": (C.c_int, [C.c_void_p, C.c_int]),
     "bmpc_cl_get": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _dp, _dp, _i32p, C.POINTER(C.c_uint64), _u32p]),
@@ -91,6 +103,19 @@ class TickConfig(C.Structure):
         super().__init__(T, l, weight_y, weight_phi, weight_steering_front, weight_steering_rear, alpha_max)
 
 
+class CrossingConfig(C.Structure):
+    """bmpc_crossing_config; defaults = the reference's config defaults (src/trajectory_point_follower.cpp:446-457)."""
+    _fields_ = [("max_velocity_crossing", C.c_float), ("stopping_distance", C.c_float), ("distance_to_stop", C.c_float),
+                ("crossing_safety_zone", C.c_float)]
+
+    def __init__(self, max_velocity_crossing=1.0, stopping_distance=0.35, distance_to_stop=1.0, crossing_safety_zone=0.05):
+        super().__init__(max_velocity_crossing, stopping_distance, distance_to_stop, crossing_safety_zone)
+
+
+LOOKUP_DISTANCE, LOOKUP_VELOCITY = 0, 1
+PID_SLOWDOWN, PID_FRONT, PID_REAR = 0, 1, 2
+
+
 class BmpcError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"bmpc error {code}: {msg}")
@@ -106,6 +131,8 @@ def lib() -> C.CDLL:
                                     "or `make -C trajectory_controller_b200/csrc -j8`")
         L = C.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
+            if os.environ.get("BMPC_LIB") and not hasattr(L, name):
+                continue                      # developer A/B builds of older sources (scripts/): newer entry points absent
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
         _lib = L
@@ -129,6 +156,14 @@ def shape_supported(S: int, I: int, N: int) -> bool:
     return bool(lib().bmpc_shape_supported(S, I, N))
 
 
+class _DeviceView:
+    """Minimal CUDA array interface wrapper around a device pointer owned by a handle."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
 class BatchedMPC:
     """`capacity` dlib::mpc<S,I,N>-compatible controllers on one GPU."""
 
@@ -137,6 +172,8 @@ class BatchedMPC:
         self.precision, self.mode = precision, mode
         self._h = C.c_void_p()
         _check(lib().bmpc_create(C.byref(self._h), S, I, N, self.capacity, precision, mode, device))
+        if os.environ.get("BMPC_SPLIT"):   # developer A/B knob (scripts/): the bmpc_set_split setting of every handle
+            self.set_split(int(os.environ["BMPC_SPLIT"]))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
@@ -166,7 +203,9 @@ class BatchedMPC:
 
     def set_split(self, enable):
         """0/False: one-kernel solve; 1/True: two-stage solve (coordinate-phase kernel + projected-gradient kernel)
-        with time slicing of small batches (default); 2: two-stage without time slicing.  Results are identical."""
+        with fairness slices of small batches, retirement of surplus warps and the symmetric-bound stage-B kernel
+        (default); 2: two-stage, every instance runs to completion in the lane that claimed it; 3: like 1 with the
+        literal stage-B kernel even where the bounds are symmetric.  Results are identical."""
         _check(lib().bmpc_set_split(self._h, int(enable)))
 
     def pattern_name(self) -> str:
@@ -260,6 +299,17 @@ class BatchedMPC:
     def sync(self):
         _check(lib().bmpc_sync(self._h))
 
+    def device_results(self):
+        """Device views (``__cuda_array_interface__`` objects, e.g. for ``torch.as_tensor(v, device="cuda")``) of the last
+        solve's results in HBM: u0 [I][capacity] in the compute type, iters uint32 (exposed as int32) [capacity],
+        status uint8 [capacity].  For callers that gather results with a collective instead of a D2H per GPU."""
+        ptrs = [C.c_void_p() for _ in range(3)]
+        _check(lib().bmpc_device_results(self._h, *[C.byref(p) for p in ptrs]))
+        ft = "<f8" if self.precision == FP64 else "<f4"
+        return (_DeviceView(ptrs[0].value, (self.I, self.capacity), ft),
+                _DeviceView(ptrs[1].value, (self.capacity,), "<i4"),
+                _DeviceView(ptrs[2].value, (self.capacity,), "|u1"))
+
     def set_stream(self, cuda_stream: int | None):
         """Borrow a caller's cudaStream_t (integer handle, e.g. torch.cuda.current_stream().cuda_stream); None/0 = own."""
         _check(lib().bmpc_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
@@ -320,16 +370,9 @@ class BatchedMPC:
         cfg = cfg or TickConfig()
         arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
         velocity = np.ascontiguousarray(velocity, dtype=np.float32)
-        dist = np.ascontiguousarray(dist, dtype=np.float32)
+        dist = None if dist is None else np.ascontiguousarray(dist, dtype=np.float32)   # None: look-ahead on the device
         B = velocity.shape[0]
-        if layout == "shared":
-            P, si, sp = arrs[0].shape[0], 0, 1
-        elif layout == "pb":
-            P, si, sp = arrs[0].shape[0], 1, B
-        elif layout == "bp":
-            P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
-        else:
-            raise ValueError(layout)
+        P, si, sp = self._poly_strides(arrs[0], layout, B)
         vm = None if v_model is None else _c64(v_model)
         npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
         out = dict(steering_front=np.empty(B), steering_rear=np.empty(B), target_speed=np.empty(B, dtype=np.float32),
@@ -341,6 +384,65 @@ class BatchedMPC:
                                           _p(out["target_speed"], _fp), _p(out["target_distance"], _fp), _p(out["state"], _u8p),
                                           _p(out["idx"], _i32p), _p(out["flag"], _u8p), _p(out["target"]), _p(out["iters"], _u32p)))
         return out
+
+    @staticmethod
+    def _poly_strides(a, layout, B):
+        if layout == "shared":
+            return a.shape[0], 0, 1
+        if layout == "pb":
+            return a.shape[0], 1, B
+        if layout == "bp":
+            return a.shape[1], a.shape[1], 1
+        raise ValueError(layout)
+
+    def fleet_tick_pid(self, velocity, dist, px, py, dx, dy, vel, layout: str = "pb", npoints=None):
+        """The non-MPC branch of cycle() (src/trajectory_point_follower.cpp:214-225) for len(velocity) vehicles."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+        velocity = np.ascontiguousarray(velocity, dtype=np.float32)
+        dist = None if dist is None else np.ascontiguousarray(dist, dtype=np.float32)
+        B = velocity.shape[0]
+        P, si, sp = self._poly_strides(arrs[0], layout, B)
+        npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+        out = dict(steering_front=np.empty(B), steering_rear=np.empty(B), target_speed=np.empty(B, dtype=np.float32),
+                   target_distance=np.empty(B, dtype=np.float32), idx=np.empty(B, dtype=np.int32), flag=np.empty(B, dtype=np.uint8))
+        _check(lib().bmpc_fleet_tick_pid(self._h, B, _p(velocity, _fp), _p(dist, _fp), P, _p(npts, _i32p),
+                                         *[_p(a, _fp) for a in arrs], si, sp, _p(out["steering_front"]), _p(out["steering_rear"]),
+                                         _p(out["target_speed"], _fp), _p(out["target_distance"], _fp),
+                                         _p(out["idx"], _i32p), _p(out["flag"], _u8p)))
+        return out
+
+    def set_lookup(self, which: int, vx, vy):
+        """lms::math::LookupTable<float, ASC> samples (LOOKUP_DISTANCE: src/...:66; LOOKUP_VELOCITY: :323); empty = none."""
+        vx = np.ascontiguousarray(vx, dtype=np.float32); vy = np.ascontiguousarray(vy, dtype=np.float32)
+        _check(lib().bmpc_set_lookup(self._h, which, len(vx), _p(vx, _fp), _p(vy, _fp)))
+
+    def lookup(self, which: int, x):
+        x = np.ascontiguousarray(x, dtype=np.float32); y = np.empty_like(x)
+        _check(lib().bmpc_lookup(self._h, which, x.shape[0], _p(x, _fp), _p(y, _fp)))
+        return y
+
+    def set_drive_mode(self, foh: bool, regelpunkt_min: float = 0.6, regelpunkt_slope: float = 0.1):
+        _check(lib().bmpc_fleet_set_drive_mode(self._h, int(foh), regelpunkt_min, regelpunkt_slope))
+
+    def set_crossing(self, cfg):
+        """CrossingConfig, or None to switch the stop-at-crossing clamp off."""
+        _check(lib().bmpc_fleet_set_crossing(self._h, None if cfg is None else C.byref(cfg)))
+
+    def set_pid(self, which: int, kp, ki, kd, dt):
+        _check(lib().bmpc_fleet_set_pid(self._h, which, kp, ki, kd, dt))
+
+    def reset_pid(self, which: int):
+        _check(lib().bmpc_fleet_reset_pid(self._h, which))
+
+    def get_pid(self, which: int, count: int):
+        i = np.empty(count, dtype=np.float32); p = np.empty(count, dtype=np.float32); f = np.empty(count, dtype=np.uint8)
+        _check(lib().bmpc_fleet_get_pid(self._h, which, count, _p(i, _fp), _p(p, _fp), _p(f, _u8p)))
+        return i, p, f
+
+    def put_pid(self, which: int, integral, prev, first):
+        i = np.ascontiguousarray(integral, dtype=np.float32); p = np.ascontiguousarray(prev, dtype=np.float32)
+        f = np.ascontiguousarray(first, dtype=np.uint8)
+        _check(lib().bmpc_fleet_put_pid(self._h, which, i.shape[0], _p(i, _fp), _p(p, _fp), _p(f, _u8p)))
 
     # ---- trajectory point ---------------------------------------------------------------------------------------------------
     def extract_points(self, px, py, dx, dy, vel, dist, npoints=None, layout: str = "shared"):
