@@ -299,6 +299,48 @@ int bmpc_fleet_tick_pid(bmpc_t* h, int64_t count, const float* velocity, const f
                         int64_t stride_instance, int64_t stride_point, double* steering_front, double* steering_rear,
                         float* target_speed, float* target_distance, int32_t* idx, uint8_t* flag);
 
+/* ---- device groups: one controller population sharded over several GPUs of this process -----------------------------
+ * SURVEY.md §8(b) (`devices[]`, `ndev` at create) and §8(e): every dlib::mpc object is independent (mpc.h:216-347 touches
+ * only its own members), so a population of `capacity` controllers is split along the instance axis over `ndev` devices.
+ * A group owns one bmpc_t and one host worker thread per device; every group call runs on all members concurrently and
+ * returns when all are done.  There is no device-to-device traffic: the only "collective" is the gather of the results
+ * into the caller's host arrays, done by each member's own D2H copy.  Arguments and host layouts are those of the
+ * single-handle call of the same name; `count` / `instance` are GLOBAL (0 .. capacity-1).
+ *
+ * Assignment of global instance i to a member is fixed at create (persistent controllers keep their state in place):
+ *   BMPC_GROUP_INTERLEAVED  member i mod ndev, local slot i / ndev — every prefix [0, count) is balanced, heavy-tailed
+ *                           iteration counts and blocked parameter sweeps are spread evenly (§8(e)); the members pack /
+ *                           unpack their strided share of the host arrays in their worker threads
+ *   BMPC_GROUP_CONTIGUOUS   member k owns [k*per, (k+1)*per), per = ceil(capacity / ndev) — the host arrays are used in
+ *                           place (no packing); balanced only when count == capacity
+ * `devices` may be NULL (devices 0 .. ndev-1) and may name a device more than once (two members then share it; used by
+ * the single-GPU tests of this layer).  Results are bit-identical to one handle solving the same instances. */
+typedef struct bmpc_group bmpc_group_t;
+#define BMPC_GROUP_INTERLEAVED 0
+#define BMPC_GROUP_CONTIGUOUS 1
+int bmpc_group_create(bmpc_group_t** out, int S, int I, int N, int64_t capacity, int precision, int mode,
+                      const int* devices, int ndev, int assignment);
+void bmpc_group_destroy(bmpc_group_t* g);
+int bmpc_group_size(bmpc_group_t* g);
+/* Member k's handle (options, kernel info, device-resident results ...); owned by the group. */
+bmpc_t* bmpc_group_member(bmpc_group_t* g, int k);
+/* How many of the global instances [0, count) member k holds (its local slots 0 .. *local_count-1) and, for the
+ * contiguous assignment, the global index of its local slot 0 (interleaved: k). */
+int bmpc_group_shard(bmpc_group_t* g, int k, int64_t count, int64_t* first, int64_t* local_count);
+int bmpc_group_set_model(bmpc_group_t* g, const double* A, const double* B, const double* C, const double* Q,
+                         const double* R, const double* lower, const double* upper, int per_instance, int64_t count);
+int bmpc_group_set_options(bmpc_group_t* g, double eps, uint64_t max_iterations);
+int bmpc_group_set_target(bmpc_group_t* g, const double* val, int time, int per_instance, int64_t count);
+int bmpc_group_reset(bmpc_group_t* g);
+/* operator() for the global instances [0, count): x0[count][S] in; u0[count][I], iters[count], status[count] out (the
+ * last two may be NULL) — H2D, solve and D2H of every member overlap with the others'. */
+int bmpc_group_solve(bmpc_group_t* g, int64_t count, const double* x0, double* u0, uint32_t* iters, uint8_t* status,
+                     unsigned flags);
+/* controls[count][N][I] of the global instances first .. first+count-1 (bmpc_get_controls). */
+int bmpc_group_get_controls(bmpc_group_t* g, int64_t first, int64_t count, double* controls);
+/* Device time of the last solve: the maximum over the members (ms). */
+int bmpc_group_last_kernel_ms(bmpc_group_t* g, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

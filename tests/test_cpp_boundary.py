@@ -40,7 +40,7 @@ def test_no_silent_cpu_fallback(built):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exe", ["test_facade", "test_module"])
+@pytest.mark.parametrize("exe", ["test_facade", "test_module", "test_group"])
 def test_cpp_boundary_on_gpu(built, exe):
     """dlib's KAT / golden values through the facade; the module driven headless, bit-equal to the CPU glue."""
     r = subprocess.run([os.path.join(built, exe)], capture_output=True, text=True, timeout=600)

@@ -81,6 +81,19 @@ SIGNATURES = {
     "bmpc_cl_init": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p] + [_dp] * 6),
     "bmpc_cl_run": (C.c_int, [C.c_void_p, C.c_int]),
     "bmpc_cl_get": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _dp, _dp, _i32p, C.POINTER(C.c_uint64), _u32p]),
+    "bmpc_group_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,
+                                    C.POINTER(C.c_int), C.c_int, C.c_int]),
+    "bmpc_group_destroy": (None, [C.c_void_p]),
+    "bmpc_group_size": (C.c_int, [C.c_void_p]),
+    "bmpc_group_member": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "bmpc_group_shard": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "bmpc_group_set_model": (C.c_int, [C.c_void_p] + [_dp] * 7 + [C.c_int, C.c_int64]),
+    "bmpc_group_set_options": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64]),
+    "bmpc_group_set_target": (C.c_int, [C.c_void_p, _dp, C.c_int, C.c_int, C.c_int64]),
+    "bmpc_group_reset": (C.c_int, [C.c_void_p]),
+    "bmpc_group_solve": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _u32p, _u8p, C.c_uint]),
+    "bmpc_group_get_controls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, _dp]),
+    "bmpc_group_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
 }
 
 
@@ -113,6 +126,7 @@ class CrossingConfig(C.Structure):
 
 
 LOOKUP_DISTANCE, LOOKUP_VELOCITY = 0, 1
+GROUP_INTERLEAVED, GROUP_CONTIGUOUS = 0, 1
 PID_SLOWDOWN, PID_FRONT, PID_REAR = 0, 1, 2
 
 
@@ -465,3 +479,82 @@ class BatchedMPC:
         _check(lib().bmpc_extract_points(self._h, B, P, _p(npts, _i32p), *[_p(a, _fp) for a in arrs], si, sp,
                                          _p(dist, _fp), _p(idx, _i32p), _p(flag, _u8p), *[_p(o, _fp) for o in outs]))
         return idx, flag, outs
+
+
+class ShardedMPC:
+    """`capacity` controllers sharded by instance over several GPUs of this process (bmpc_group_*, include/bmpc.h):
+    one handle + one host thread per device inside libbmpc, results gathered into the caller's arrays.  `devices`
+    may repeat a device (two members share it)."""
+
+    def __init__(self, S: int, I: int, N: int, capacity: int, precision: int = FP64, mode: int = EXACT, devices=None,
+                 assignment: int = GROUP_INTERLEAVED):
+        self.S, self.I, self.N, self.capacity = S, I, N, int(capacity)
+        self._g = C.c_void_p()
+        if devices is None:
+            dv, nd = None, 0
+        else:
+            nd = len(devices); dv = (C.c_int * nd)(*devices)
+        _check(lib().bmpc_group_create(C.byref(self._g), S, I, N, self.capacity, precision, mode, dv, nd, assignment))
+
+    def close(self):
+        if getattr(self, "_g", None) is not None and self._g:
+            lib().bmpc_group_destroy(self._g)
+            self._g = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def size(self) -> int:
+        return lib().bmpc_group_size(self._g)
+
+    def shard(self, k: int, count: int | None = None):
+        f, n = C.c_int64(), C.c_int64()
+        _check(lib().bmpc_group_shard(self._g, k, self.capacity if count is None else count, C.byref(f), C.byref(n)))
+        return f.value, n.value
+
+    def set_model(self, model, per_instance: bool = False):
+        g = (lambda k: model[k]) if isinstance(model, dict) else (lambda k: getattr(model, k))
+        arrs = [_c64(g(k)) for k in ("A", "B", "C", "Q", "R", "lower", "upper")]
+        count = arrs[0].shape[0] if per_instance else 1
+        _check(lib().bmpc_group_set_model(self._g, *[_p(a) for a in arrs], int(per_instance), count))
+        return self
+
+    def set_options(self, eps: float, max_iter: int):
+        _check(lib().bmpc_group_set_options(self._g, eps, max_iter))
+
+    def set_target(self, val, time: int = -1):
+        v = _c64(val)
+        per = v.ndim == 2
+        _check(lib().bmpc_group_set_target(self._g, _p(v), time, int(per), v.shape[0] if per else 0))
+
+    def reset(self):
+        _check(lib().bmpc_group_reset(self._g))
+
+    def solve(self, x0, warm: bool = False, keep_controls: bool = False, out=None):
+        x = _c64(x0)
+        B = x.shape[0]
+        if out is None:
+            u0 = np.empty((B, self.I)); it = np.empty(B, dtype=np.uint32); st = np.empty(B, dtype=np.uint8)
+        else:
+            u0, it, st = out
+        flags = (WARM if warm else 0) | (KEEP_CONTROLS if keep_controls else 0)
+        _check(lib().bmpc_group_solve(self._g, B, _p(x), _p(u0), _p(it, _u32p), _p(st, _u8p), flags))
+        return u0, it, st
+
+    __call__ = solve
+
+    def get_controls(self, count: int | None = None, first: int = 0):
+        count = self.capacity - first if count is None else count
+        out = np.zeros((count, self.N, self.I))
+        _check(lib().bmpc_group_get_controls(self._g, first, count, _p(out)))
+        return out
+
+    def last_kernel_ms(self) -> float:
+        ms = C.c_float()
+        _check(lib().bmpc_group_last_kernel_ms(self._g, C.byref(ms)))
+        return ms.value
