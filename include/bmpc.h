@@ -165,6 +165,17 @@ int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints,
                         int64_t stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* out_px,
                         float* out_py, float* out_dx, float* out_dy, float* out_vel);
 
+/* getTrajectoryPoint for a whole horizon ("sample the trajectory at N lookahead distances and
+ * set_target(val, t) per step"; dlib's per-step targets, mpc.h:142-170, contract mpc_abstract.h:180-206).  Step t of
+ * instance b asks for the distance d_t = d0[b] + (float)t * step[b] (float multiply and add, each rounded on its own);
+ * the result for step t is exactly what bmpc_extract_points returns for that distance — the device produces all
+ * `steps` points in one sequential scan of the polyline.  step[b] must be >= 0.  Polyline arguments as for
+ * bmpc_extract_points; outputs are instance-major [count][steps]. */
+int bmpc_extract_horizon(bmpc_t* h, int64_t count, int P, const int32_t* npoints, const float* px, const float* py,
+                         const float* dx, const float* dy, const float* vel, int64_t stride_instance,
+                         int64_t stride_point, const float* d0, const float* step, int steps, int32_t* idx,
+                         uint8_t* flag, float* out_px, float* out_py, float* out_dx, float* out_dy, float* out_vel);
+
 /* ---- closed loop on the device  (BASELINE.json configs[4]) ------------------------------------
  * Every tick, for every vehicle, without a host round trip:
  *   sample the world path into a vehicle-frame polyline of P float points (what the TRAJECTORY channel carries)
@@ -198,6 +209,13 @@ typedef struct bmpc_cl_config {
  * act0[count][2] = delta, delta_dot (NULL = zeros).  Resets the controllers (fresh dlib::mpc objects). */
 int bmpc_cl_init(bmpc_t* h, int64_t count, const bmpc_cl_config* cfg, const double* path_x, const double* path_y,
                  const double* path_tx, const double* path_ty, const double* pose0, const double* act0);
+/* A target per horizon step instead of one for all steps (§8(f) rank 2): every tick the vehicle-frame polyline is
+ * sampled at d_t = d0 + (float)t * step, t = 0 .. N-1 (see bmpc_extract_horizon) and target[t] = (point_t.y,
+ * atan(dir_t.y/dir_t.x), 0, 0) is written for every step (dlib: set_target(val, t), mpc.h:142-155) before the solve.
+ * d0, step in metres, used as float, step >= 0; the natural choice is d0 = step = T*v (state i+1 of the prediction lies
+ * (i+1)*T*v ahead).  enable = 0: back to the reference's single target at `lookahead` (src/...:368-371).  Call after
+ * bmpc_cl_init; bmpc_cl_get then reports target / idx of horizon step 0. */
+int bmpc_cl_set_horizon_targets(bmpc_t* h, int enable, double d0, double step);
 /* `ticks` control ticks for all vehicles; kernels only, synchronous on return. */
 int bmpc_cl_run(bmpc_t* h, int ticks);
 /* State after the last tick; any pointer may be NULL.  pose[count][4], act[count][2], u0[count] (last command),

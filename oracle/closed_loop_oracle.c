@@ -28,6 +28,8 @@ typedef struct {
     int32_t* idx;
     uint64_t* iters_total;
     uint32_t* iters_max;
+    int horizon_targets;          /* 1: a target per horizon step (orc_extract_horizon), 0: one target for all steps */
+    float h_d0, h_step;
 } job_t;
 
 static void* worker(void* arg)
@@ -59,13 +61,30 @@ static void* worker(void* arg)
                 vl[i] = (float)j->v;
             }
             orc_point pt;
-            orc_extract_point(px, py, dx, dy, vl, 1, n, d, &pt);
-            const double y_soll = (double)pt.pos_y;
-            double phi;
-            if (pt.dir_x > 0.0f) phi = orc_harness_atan((double)pt.dir_y / (double)pt.dir_x);
-            else phi = pt.dir_y >= 0.0f ? 1.5707963267948966 : -1.5707963267948966;
-            const double tgt[4] = {y_soll, phi, 0.0, 0.0};
-            orc_mpc_set_target(m, tgt, -1);
+            double y_soll = 0.0, phi = 0.0;
+            if (!j->horizon_targets) {
+                orc_extract_point(px, py, dx, dy, vl, 1, n, d, &pt);
+                y_soll = (double)pt.pos_y;
+                if (pt.dir_x > 0.0f) phi = orc_harness_atan((double)pt.dir_y / (double)pt.dir_x);
+                else phi = pt.dir_y >= 0.0f ? 1.5707963267948966 : -1.5707963267948966;
+                const double tgt[4] = {y_soll, phi, 0.0, 0.0};
+                orc_mpc_set_target(m, tgt, -1);
+            } else {
+                /* set_target(val, t) per horizon step (mpc.h:142-155) from the look-ahead points at
+                 * d_t = h_d0 + t * h_step; the reported target / idx are those of step 0 */
+                orc_point pts[ORC_MAX_N];
+                orc_extract_horizon(px, py, dx, dy, vl, 1, n, j->h_d0, j->h_step, j->N, pts);
+                for (int h = j->N - 1; h >= 0; --h) {
+                    const double ys = (double)pts[h].pos_y;
+                    double ph;
+                    if (pts[h].dir_x > 0.0f) ph = orc_harness_atan((double)pts[h].dir_y / (double)pts[h].dir_x);
+                    else ph = pts[h].dir_y >= 0.0f ? 1.5707963267948966 : -1.5707963267948966;
+                    const double tgt[4] = {ys, ph, 0.0, 0.0};
+                    orc_mpc_set_target(m, tgt, h);
+                    y_soll = ys; phi = ph;
+                }
+                pt = pts[0];
+            }
             const double x0[4] = {0.0, 0.0, de, dd};
             double u;
             orc_mpc_step(m, x0, &u);
@@ -98,13 +117,24 @@ int orc_closed_loop(long count, int N, const double* A, const double* B, const d
                     double* act, double* u0, double* target, int32_t* idx, uint64_t* iters_total,
                     uint32_t* iters_max, int nthreads)
 {
+    return orc_closed_loop_h(count, N, A, B, C, Q, R, lo, hi, eps, max_iter, v, T, l, lookahead, P, npath, path_x, path_y,
+                             path_tx, path_ty, ticks, pose, act, u0, target, idx, iters_total, iters_max, nthreads, 0, 0.0f, 0.0f);
+}
+
+int orc_closed_loop_h(long count, int N, const double* A, const double* B, const double* C, const double* Q,
+                      const double* R, const double* lo, const double* hi, double eps, unsigned long max_iter,
+                      double v, double T, double l, double lookahead, int P, int npath, const double* path_x,
+                      const double* path_y, const double* path_tx, const double* path_ty, int ticks, double* pose,
+                      double* act, double* u0, double* target, int32_t* idx, uint64_t* iters_total,
+                      uint32_t* iters_max, int nthreads, int horizon_targets, float h_d0, float h_step)
+{
     if (count < 1 || N < 1 || N > ORC_MAX_N || P < 1 || npath < P || nthreads < 1) return -1;
     if (nthreads > 256) nthreads = 256;
     pthread_t th[256]; job_t jobs[256];
     for (int k = 0; k < nthreads; ++k) {
         job_t j = {count * k / nthreads, count * (k + 1) / nthreads, N, P, npath, ticks, A, B, C, Q, R, lo, hi,
                    path_x, path_y, path_tx, path_ty, eps, v, T, l, lookahead, max_iter, pose, act, u0, target, idx,
-                   iters_total, iters_max};
+                   iters_total, iters_max, horizon_targets, h_d0, h_step};
         jobs[k] = j;
         pthread_create(&th[k], 0, worker, &jobs[k]);
     }

@@ -25,6 +25,15 @@ int orc_closed_loop(long count, int N, const double* A, const double* B, const d
                     const double* path_y, const double* path_tx, const double* path_ty, int ticks, double* pose,
                     double* act, double* u0, double* target, int32_t* idx, uint64_t* iters_total,
                     uint32_t* iters_max, int nthreads);
+/* The same loop with a target per horizon step (horizon_targets = 1): every tick the polyline is sampled at
+ * d_t = h_d0 + t * h_step (orc_extract_horizon) and target[t] = (pos.y, atan(dir.y/dir.x), 0, 0) is set with
+ * set_target(val, t) (mpc.h:142-155) before the solve; `target` / `idx` report step 0 of the last tick. */
+int orc_closed_loop_h(long count, int N, const double* A, const double* B, const double* C, const double* Q,
+                      const double* R, const double* lo, const double* hi, double eps, unsigned long max_iter,
+                      double v, double T, double l, double lookahead, int P, int npath, const double* path_x,
+                      const double* path_y, const double* path_tx, const double* path_ty, int ticks, double* pose,
+                      double* act, double* u0, double* target, int32_t* idx, uint64_t* iters_total,
+                      uint32_t* iters_max, int nthreads, int horizon_targets, float h_d0, float h_step);
 #ifdef __cplusplus
 }
 #endif

@@ -51,3 +51,40 @@ void orc_extract_batch(long count, int P, const int32_t* npoints, const float* p
         out_px[b] = p.pos_x; out_py[b] = p.pos_y; out_dx[b] = p.dir_x; out_dy[b] = p.dir_y; out_vel[b] = p.vel;
     }
 }
+
+void orc_extract_horizon(const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                         long stride, int P, float d0, float step, int steps, orc_point* out)
+{
+    int t = 0;                                            /* next horizon step without a point */
+    if (P <= 0) {                                         /* :394-407 for every step */
+        for (; t < steps; ++t) {
+            const float d = d0 + (float)t * step;
+            out[t].pos_x = d; out[t].pos_y = 0.0f; out[t].dir_x = 1.0f; out[t].dir_y = 0.0f; out[t].vel = 0.0f;
+            out[t].idx = -1; out[t].flag = ORC_PT_EMPTY;
+        }
+        return;
+    }
+    float cur = 0.0f;                                     /* :423 */
+    for (int i = 1; i < P && t < steps; ++i) {            /* :424 */
+        const float bx = px[(i - 1) * stride], by = py[(i - 1) * stride];
+        const float tx = px[i * stride], ty = py[i * stride];
+        const float ex = bx - tx, ey = by - ty;
+        const float len = sqrtf(ex * ex + ey * ey);       /* :427 */
+        cur = cur + len;
+        for (; t < steps; ++t) {                          /* every step whose distance this segment is the first to exceed */
+            const float d = d0 + (float)t * step;
+            if (!(cur > d)) break;                        /* :428 strict */
+            const float delta = cur - d;                  /* :431 */
+            const float nx = ex / len, ny = ey / len;     /* :432 */
+            const float ax = nx * delta, ay = ny * delta;
+            out[t].pos_x = tx + ax; out[t].pos_y = ty + ay;   /* :433-434 */
+            out[t].dir_x = dx[i * stride]; out[t].dir_y = dy[i * stride]; out[t].vel = vel[i * stride];
+            out[t].idx = i; out[t].flag = ORC_PT_INTERPOLATED;
+        }
+    }
+    const long l = (long)(P - 1) * stride;                /* :439-442 for the steps the polyline is too short for */
+    for (; t < steps; ++t) {
+        out[t].pos_x = px[l]; out[t].pos_y = py[l]; out[t].dir_x = dx[l]; out[t].dir_y = dy[l]; out[t].vel = vel[l];
+        out[t].idx = P - 1; out[t].flag = ORC_PT_LAST;
+    }
+}

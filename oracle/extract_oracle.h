@@ -42,6 +42,16 @@ void orc_extract_batch(long count, int P, const int32_t* npoints, const float* p
                        const float* dx, const float* dy, const float* vel, long stride_instance,
                        long stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* out_px,
                        float* out_py, float* out_dx, float* out_dy, float* out_vel);
+
+/* Look-ahead points for `steps` horizon steps of one polyline ("sample the trajectory at N
+ * lookahead distances and set_target(val, t) per step"; dlib's per-step targets, mpc.h:142-170).  Step t asks
+ * getTrajectoryPoint (:392-443) for the distance d_t = d0 + (float)t * step — one float multiply and one float add,
+ * each rounded on its own.  DEFINITION: out[t] == orc_extract_point(..., d_t).  orc_extract_horizon restates that as
+ * the single sequential scan the device runs (needs step >= 0 so that the d_t ascend; the arc length `cur` is the
+ * same float sum for every t, so the first segment with cur > d_t is the same one); tests/test_oracle.py checks the
+ * two against each other. */
+void orc_extract_horizon(const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                         long stride, int P, float d0, float step, int steps, orc_point* out /* [steps] */);
 #ifdef __cplusplus
 }
 #endif

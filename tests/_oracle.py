@@ -94,21 +94,24 @@ class Oracle:
 
     # ---- closed loop (oracle/closed_loop_oracle.c) ------------------------------------------------------------------
     def closed_loop(self, model, N, path, pose0, ticks, act0=None, v=1.0, T=0.1, l=0.21, lookahead=None, P=64,
-                    eps=0.01, max_iter=10000, nthreads=8):
+                    eps=0.01, max_iter=10000, nthreads=8, horizon=None):
+        """horizon = (d0, step): a target per horizon step sampled at d_t = d0 + t*step (orc_closed_loop_h)."""
         ma = _ModelArgs(model)
         px, py, tx, ty = (_c64(a) for a in path)
         pose = _c64(pose0).copy(); n = pose.shape[0]
         act = np.zeros((n, 2)) if act0 is None else _c64(act0).copy()
         u0 = np.zeros(n); tgt = np.zeros((n, 2)); idx = np.zeros(n, dtype=np.int32)
         itot = np.zeros(n, dtype=np.uint64); imax = np.zeros(n, dtype=np.uint32)
-        f = self.lib.orc_closed_loop
+        f = self.lib.orc_closed_loop_h
         f.restype = C.c_int
         f.argtypes = [C.c_long, C.c_int] + [_dp] * 7 + [C.c_double, C.c_ulong] + [C.c_double] * 4 + [C.c_int, C.c_int] + \
-            [_dp] * 4 + [C.c_int] + [_dp] * 4 + [C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.c_int]
+            [_dp] * 4 + [C.c_int] + [_dp] * 4 + [C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.c_int] + \
+            [C.c_int, C.c_float, C.c_float]
+        hz = (0, 0.0, 0.0) if horizon is None else (1, float(np.float32(horizon[0])), float(np.float32(horizon[1])))
         rc = f(n, N, *ma.ptrs, eps, max_iter, v, T, l, (0.6 + 0.1 * v) if lookahead is None else lookahead, P,
                px.shape[0], _d(px), _d(py), _d(tx), _d(ty), ticks, _d(pose), _d(act), _d(u0), _d(tgt),
                idx.ctypes.data_as(C.POINTER(C.c_int32)), itot.ctypes.data_as(C.POINTER(C.c_uint64)),
-               imax.ctypes.data_as(C.POINTER(C.c_uint32)), nthreads)
+               imax.ctypes.data_as(C.POINTER(C.c_uint32)), nthreads, *hz)
         if rc != 0:
             raise ValueError("oracle: bad closed-loop arguments")
         return dict(pose=pose, act=act, u0=u0, target=tgt, idx=idx, iters_total=itot, iters_max=imax)
@@ -157,6 +160,35 @@ class Oracle:
         return sf, sr, td
 
     # ---- point extraction ---------------------------------------------------------------------------------
+    def extract_horizon(self, px, py, dx, dy, vel, d0, step, steps, npoints=None, layout="shared"):
+        """orc_extract_horizon per instance: (idx[B][steps], flag[B][steps], (px, py, dx, dy, vel)[B][steps])."""
+        class Pt(C.Structure):
+            _fields_ = [("pos_x", C.c_float), ("pos_y", C.c_float), ("dir_x", C.c_float), ("dir_y", C.c_float), ("vel", C.c_float),
+                        ("idx", C.c_int32), ("flag", C.c_uint8)]
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+        d0 = np.ascontiguousarray(d0, dtype=np.float32); step = np.ascontiguousarray(step, dtype=np.float32)
+        B = d0.shape[0]
+        if layout == "shared":
+            P, si, sp = arrs[0].shape[0], 0, 1
+        elif layout == "pb":
+            P, si, sp = arrs[0].shape[0], 1, B
+        else:
+            P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
+        f = self.lib.orc_extract_horizon
+        f.restype = None
+        f.argtypes = [C.c_void_p] * 5 + [C.c_long, C.c_int, C.c_float, C.c_float, C.c_int, C.POINTER(Pt)]
+        idx = np.zeros((B, steps), dtype=np.int32); flag = np.zeros((B, steps), dtype=np.uint8)
+        outs = [np.zeros((B, steps), dtype=np.float32) for _ in range(5)]
+        pts = (Pt * steps)()
+        for b in range(B):
+            n = P if npoints is None else min(int(npoints[b]), P)
+            f(*[a.ctypes.data + 4 * b * si for a in arrs], sp, n, float(d0[b]), float(step[b]), steps, pts)
+            for t in range(steps):
+                idx[b, t] = pts[t].idx; flag[b, t] = pts[t].flag
+                for o, k in zip(outs, ("pos_x", "pos_y", "dir_x", "dir_y", "vel")):
+                    o[b, t] = getattr(pts[t], k)
+        return idx, flag, tuple(outs)
+
     def extract(self, px, py, dx, dy, vel, dist, npoints=None, layout="shared"):
         """layout 'shared': component arrays [P]; 'pb': [P][B] (point-major); 'bp': [B][P]."""
         arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]

@@ -74,3 +74,44 @@ def test_closed_loop_full_size_properties():
     sub = a["pose"][:: 64]
     d = np.min(np.hypot(sub[:, 0, None] - path[0][None, :], sub[:, 1, None] - path[1][None, :]), axis=1)
     assert np.all(d < 0.2), d.max()
+
+
+def test_oracle_horizon_targets_track_better(oracle):
+    """A target per horizon step follows the sine path more tightly than one look-ahead target."""
+    path = W.sine_world_path()
+    pose0 = W.closed_loop_poses(48, 45, path)
+    bike = W.bicycle4_model()
+    def err(r):
+        return np.min(np.hypot(r["pose"][:, 0, None] - path[0][None, :], r["pose"][:, 1, None] - path[1][None, :]), axis=1)
+    a = oracle.closed_loop(bike, 30, path, pose0, ticks=200)
+    b = oracle.closed_loop(bike, 30, path, pose0, ticks=200, horizon=(0.1, 0.1))
+    assert err(b).mean() < err(a).mean()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,count,ticks,hz", [(30, 700, 36, (0.1, 0.1)), (10, 900, 90, (0.7, 0.05)), (30, 300, 20, (0.6, 0.0))])
+def test_closed_loop_horizon_targets_match_oracle(oracle, N, count, ticks, hz):
+    """The loop with per-step targets sampled on the device (k_cl_prepare_horizon -> target ring -> warm solve) against
+    the CPU restatement with set_target(val, t) per step (orc_closed_loop_h): bit for bit."""
+    from trajectory_controller_b200.engine import BatchedMPC
+    path = W.sine_world_path()
+    pose0 = W.closed_loop_poses(count, 46, path)
+    bike = W.bicycle4_model()
+    want = oracle.closed_loop(bike, N, path, pose0, ticks=ticks, horizon=hz)
+    with BatchedMPC(4, 1, N, count) as eng:
+        eng.set_model(bike)
+        eng.cl_init(path, pose0)
+        eng.cl_set_horizon_targets(True, *hz)
+        eng.cl_run(ticks // 3)
+        eng.cl_run(ticks - ticks // 3)
+        got = eng.cl_get()
+        # switching back gives the reference's single-target loop again
+        eng.cl_init(path, pose0)
+        eng.cl_run(5)
+        plain = eng.cl_get()
+    for k in ("pose", "act", "u0", "target"):
+        assert same_values(got[k], want[k]), k
+    assert np.array_equal(got["idx"], want["idx"])
+    assert np.array_equal(got["iters_total"], want["iters_total"]) and np.array_equal(got["iters_max"], want["iters_max"])
+    ref5 = oracle.closed_loop(bike, N, path, pose0, ticks=5)
+    assert same_values(plain["pose"], ref5["pose"])

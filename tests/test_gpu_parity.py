@@ -357,6 +357,41 @@ def test_extract_points_vs_oracle(oracle):
 
 
 # ------------------------------------------------------------------------------------------ two-stage solve
+def test_extract_horizon_vs_oracle(oracle):
+    """bmpc_extract_horizon (one scan, N look-ahead distances) against the restatement, all three layouts, ragged and
+    empty polylines, steps from 1 to 100 (shared-memory tile sizes), step 0."""
+    rng = np.random.default_rng(21)
+    B, P = 777, 37
+    ang = np.cumsum(rng.normal(0, 0.15, (B, P)), axis=1)
+    seg = rng.uniform(0.02, 0.3, (B, P))
+    arr = [np.cumsum(seg * np.cos(ang), 1), np.cumsum(seg * np.sin(ang), 1), np.cos(ang), np.sin(ang), rng.uniform(0, 2, (B, P))]
+    arr = [a.astype(np.float32) for a in arr]
+    npts = rng.integers(0, P + 1, B).astype(np.int32); npts[:5] = [0, 1, 2, P, P]
+    d0 = rng.uniform(-0.1, 1.5, B).astype(np.float32); step = rng.choice([0.0, 0.05, 0.1, 0.4], B).astype(np.float32)
+    with BatchedMPC(4, 1, 30, B) as eng:
+        for steps in (1, 30, 100):
+            want = oracle.extract_horizon(*arr, d0, step, steps, npoints=npts, layout="bp")
+            for layout, a in (("bp", arr), ("pb", [np.ascontiguousarray(x.T) for x in arr])):
+                got = eng.extract_horizon(*a, d0, step, steps, npoints=npts, layout=layout)
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (steps, layout)
+                for g, w in zip(got[2], want[2]):
+                    assert np.array_equal(g.view(np.uint32), w.view(np.uint32)), (steps, layout)
+        one = [x[3] for x in arr]
+        want = oracle.extract_horizon(*one, d0, step, 30)
+        got = eng.extract_horizon(*one, d0, step, 30, layout="shared")
+        assert np.array_equal(got[0], want[0])
+        for g, w in zip(got[2], want[2]):
+            assert np.array_equal(g.view(np.uint32), w.view(np.uint32))
+        # step t of the horizon call == the single-point call at d_t
+        t = 7
+        dt = (d0 + np.float32(t) * step).astype(np.float32)
+        i1, f1, o1 = eng.extract_points(*arr, dt, npoints=npts, layout="bp")
+        got = eng.extract_horizon(*arr, d0, step, 30, npoints=npts, layout="bp")
+        assert np.array_equal(got[0][:, t], i1) and np.array_equal(got[2][1][:, t].view(np.uint32), o1[1].view(np.uint32))
+        with pytest.raises(Exception):
+            eng.extract_horizon(*arr, d0, -np.abs(step) - 1, 30, layout="bp")
+
+
 @pytest.mark.parametrize("shape", ["bike30", "bike30_pim", "bike60", "kat30", "tobi4", "dense427"])
 def test_split_solve_equals_one_kernel(shape):
     """bmpc_set_split: stage A (set-up + coordinate phase) + stage B (projected-gradient kernel, pg_kernel.cuh) must

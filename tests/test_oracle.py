@@ -227,3 +227,35 @@ def test_extract_oracle_edges(oracle):
     for o1, o2 in zip(a[2], b[2]):
         assert np.array_equal(o1.view(np.uint32), o2.view(np.uint32))
     assert a[0][0] == -1 and a[1][0] == 2 and a[2][0][0] == d[0]
+
+
+def test_extract_horizon_is_n_independent_lookups(oracle):
+    """oracle/extract_oracle.c: the one-scan horizon extraction equals getTrajectoryPoint asked once per step with
+    d_t = d0 + t*step (float ops rounded separately) — incl. several steps in one segment, the last-point fallback,
+    empty and one-point polylines, step 0 and a NaN distance."""
+    rng = np.random.default_rng(11)
+    for trial in range(60):
+        P = int(rng.integers(0, 40))
+        ang = np.cumsum(rng.normal(0, 0.2, max(P, 1)))
+        seg = rng.uniform(0.01, 0.5, max(P, 1))
+        px = np.cumsum(seg * np.cos(ang)).astype(np.float32)[:P]; py = np.cumsum(seg * np.sin(ang)).astype(np.float32)[:P]
+        dx = np.cos(ang).astype(np.float32)[:P]; dy = np.sin(ang).astype(np.float32)[:P]
+        vel = rng.uniform(0, 2, max(P, 1)).astype(np.float32)[:P]
+        d0 = np.float32(rng.uniform(-0.2, 2.0)); step = np.float32(rng.choice([0.0, 0.03, 0.1, 0.37, 1.5]))
+        if trial == 7:
+            d0 = np.float32(np.nan)
+        steps = int(rng.integers(1, 40))
+        if P == 0:
+            z = np.zeros(1, dtype=np.float32)
+            idx, flag, outs = oracle.extract_horizon(z, z, z, z, z, [d0], [step], steps, npoints=[0])
+        else:
+            idx, flag, outs = oracle.extract_horizon(px, py, dx, dy, vel, [d0], [step], steps)
+        for t in range(steps):
+            d = np.float32(d0 + np.float32(np.float32(t) * step))
+            if P == 0:
+                i1, f1, o1 = oracle.extract(z, z, z, z, z, np.array([d], dtype=np.float32), npoints=[0])
+            else:
+                i1, f1, o1 = oracle.extract(px, py, dx, dy, vel, np.array([d], dtype=np.float32))
+            assert idx[0, t] == i1[0] and flag[0, t] == f1[0], (trial, t)
+            for a, b in zip(outs, o1):
+                assert a[0, t].view(np.uint32) == b[0].view(np.uint32) or (np.isnan(a[0, t]) and np.isnan(b[0])), (trial, t)

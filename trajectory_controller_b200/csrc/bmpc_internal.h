@@ -49,6 +49,11 @@ cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const
                            long long stride_point, const float* dist, int32_t* idx, uint8_t* flag, float* opx,
                            float* opy, float* odx, float* ody, float* ovel, cudaStream_t st);
 
+cudaError_t launch_extract_horizon(long long count, int P, const int32_t* npoints, const float* px, const float* py,
+                                   const float* dx, const float* dy, const float* vel, long long stride_instance,
+                                   long long stride_point, const float* d0, const float* step, int steps, int32_t* idx,
+                                   uint8_t* flag, float* opx, float* opy, float* odx, float* ody, float* ovel, cudaStream_t st);
+
 const ShapeOps* find_shape(int S, int I, int N);
 const ShapeOps* select_pattern(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
                                long long count, bool as_float);
@@ -122,4 +127,6 @@ struct bmpc_handle {
     bmpc::DevBuf cl_idx;          // int32 [cap]
     bmpc::DevBuf cl_itot;         // uint64 [cap]
     bmpc::DevBuf cl_imax;         // uint32 [cap]
+    bool cl_horizon = false;      // a target per horizon step (bmpc_cl_set_horizon_targets)
+    float cl_h_d0 = 0.f, cl_h_step = 0.f;
 };

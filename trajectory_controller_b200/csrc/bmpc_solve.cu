@@ -397,4 +397,48 @@ int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints,
     return BMPC_OK;
 }
 
+int bmpc_extract_horizon(bmpc_t* h, int64_t count, int P, const int32_t* npoints, const float* px, const float* py,
+                         const float* dx, const float* dy, const float* vel, int64_t stride_instance,
+                         int64_t stride_point, const float* d0, const float* step, int steps, int32_t* idx,
+                         uint8_t* flag, float* out_px, float* out_py, float* out_dx, float* out_dy, float* out_vel)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_extract_horizon: null handle");
+    if (count < 1 || P < 0 || steps < 1 || !d0 || !step || !idx || !flag || !out_px || !out_py || !out_dx || !out_dy || !out_vel)
+        return fail(BMPC_E_INVALID, "bmpc_extract_horizon: bad argument");
+    if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, "bmpc_extract_horizon: null trajectory array");
+    if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, "bmpc_extract_horizon: negative stride");
+    for (int64_t b = 0; b < count; ++b)
+        if (!(step[b] >= 0.0f)) return fail(BMPC_E_INVALID, "bmpc_extract_horizon: step must be >= 0 (ascending distances)");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    const size_t nflt = P > 0 ? (size_t)((count - 1) * stride_instance + (int64_t)(P - 1) * stride_point + 1) : 0;
+    const float* src[5] = {px, py, dx, dy, vel};
+    for (int a = 0; a < 5; ++a) {
+        BMPC_CUDA(h->ex[a].reserve(nflt * 4 + 4));
+        if (nflt) BMPC_CUDA(cudaMemcpyAsync(h->ex[a].p, src[a], nflt * 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    BMPC_CUDA(h->ex[5].reserve((size_t)count * 8));                       // d0 | step
+    BMPC_CUDA(cudaMemcpyAsync(h->ex[5].p, d0, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    BMPC_CUDA(cudaMemcpyAsync((float*)h->ex[5].p + count, step, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    if (npoints) {
+        BMPC_CUDA(h->ex[6].reserve((size_t)count * 4));
+        BMPC_CUDA(cudaMemcpyAsync(h->ex[6].p, npoints, (size_t)count * 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    const size_t n = (size_t)count * steps;
+    for (int a = 7; a < 14; ++a) BMPC_CUDA(h->ex[a].reserve(n * 4));
+    BMPC_CUDA(launch_extract_horizon(count, P, npoints ? (const int32_t*)h->ex[6].p : nullptr, (const float*)h->ex[0].p,
+                                     (const float*)h->ex[1].p, (const float*)h->ex[2].p, (const float*)h->ex[3].p,
+                                     (const float*)h->ex[4].p, stride_instance, stride_point, (const float*)h->ex[5].p,
+                                     (const float*)h->ex[5].p + count, steps, (int32_t*)h->ex[7].p, (uint8_t*)h->ex[8].p,
+                                     (float*)h->ex[9].p, (float*)h->ex[10].p, (float*)h->ex[11].p, (float*)h->ex[12].p,
+                                     (float*)h->ex[13].p, h->stream));
+    h->launches++;
+    BMPC_CUDA(cudaMemcpyAsync(idx, h->ex[7].p, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaMemcpyAsync(flag, h->ex[8].p, n, cudaMemcpyDeviceToHost, h->stream));
+    float* outs[5] = {out_px, out_py, out_dx, out_dy, out_vel};
+    for (int a = 0; a < 5; ++a)
+        BMPC_CUDA(cudaMemcpyAsync(outs[a], h->ex[9 + a].p, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    return BMPC_OK;
+}
+
 }  // extern "C"

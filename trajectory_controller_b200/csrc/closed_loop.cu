@@ -40,6 +40,10 @@ struct ClParams {
     const double* pose;      // [4][stride]
     double* tgt_dbg;         // [2][stride]
     int32_t* idx_dbg;
+    // a target per horizon step (bmpc_cl_set_horizon_targets): N steps at d_t = h_d0 + t*h_step, written to the ring
+    // [N][4][stride] whose physical slot of step 0 is `head`
+    int N, head;
+    float h_d0, h_step;
 };
 
 // One thread per vehicle.  The arc-length scan is sequential per polyline (float sum, reference :423-427), so a
@@ -100,6 +104,73 @@ __global__ void k_cl_prepare(ClParams q, T* __restrict__ x0, T* __restrict__ tar
     q.idx_dbg[b] = ri;
 }
 
+// The same tick preparation with a target per horizon step: one sequential scan of the
+// vehicle-frame polyline yields the look-ahead point of every step (see k_extract_horizon, layout_kernels.cu — the point
+// of step t is getTrajectoryPoint(d_t)), and target[t] = (point_t.y, atan(dir_t.y/dir_t.x), 0, 0) goes straight into
+// the solver's target ring (dlib: set_target(val, t), mpc.h:142-155).
+template <typename T>
+__global__ void k_cl_prepare_horizon(ClParams q, T* __restrict__ x0, T* __restrict__ target)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= q.count) return;
+    const double X = q.pose[b], Y = q.pose[q.stride + b], c = q.pose[2 * q.stride + b], s = q.pose[3 * q.stride + b];
+    int lo = 0, hi = q.npath;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (q.path_x[mid] > X) hi = mid; else lo = mid + 1; }
+    int k0 = lo;
+    if (k0 > q.npath - q.P) k0 = q.npath - q.P;
+    if (k0 < 0) k0 = 0;
+    const int n = q.P < q.npath - k0 ? q.P : q.npath - k0;
+
+    auto vx = [&](int k) { const double dx = dsub(q.path_x[k], X), dy = dsub(q.path_y[k], Y); return (float)dadd(dmul(c, dx), dmul(s, dy)); };
+    auto vy = [&](int k) { const double dx = dsub(q.path_x[k], X), dy = dsub(q.path_y[k], Y); return (float)dsub(dmul(c, dy), dmul(s, dx)); };
+    auto dist_of = [&](int t) { return __fadd_rn(q.h_d0, __fmul_rn((float)t, q.h_step)); };
+    // target of step t from the point's y and the world tangent at path index src (src < 0: the default direction (1, 0))
+    auto put = [&](int t, float ry, int src, int ri) {
+        float fdx = 1.0f, fdy = 0.0f;
+        if (src >= 0) {
+            const double tx = q.path_tx[src], ty = q.path_ty[src];
+            fdx = (float)dadd(dmul(c, tx), dmul(s, ty));
+            fdy = (float)dsub(dmul(c, ty), dmul(s, tx));
+        }
+        const double y_soll = (double)ry;
+        double phi;
+        if (fdx > 0.0f) phi = harness_atan(ddiv((double)fdy, (double)fdx));
+        else phi = fdy >= 0.0f ? 1.5707963267948966 : -1.5707963267948966;
+        int ph = q.head + t; if (ph >= q.N) ph -= q.N;
+        T* row = target + (long long)ph * 4 * q.stride + b;
+        row[0] = (T)y_soll; row[q.stride] = (T)phi; row[2 * q.stride] = T(0); row[3 * q.stride] = T(0);
+        if (t == 0) { q.tgt_dbg[b] = y_soll; q.tgt_dbg[q.stride + b] = phi; q.idx_dbg[b] = ri; }
+    };
+    int t = 0;
+    if (n <= 0) {
+        for (; t < q.N; ++t) put(t, 0.0f, -1, -1);
+    } else {
+        float cur = 0.0f, bx = vx(k0), by = vy(k0);
+        float d = dist_of(0);
+        for (int i = 1; i < n && t < q.N; ++i) {
+            const float tx = vx(k0 + i), ty = vy(k0 + i);
+            const float ex = __fsub_rn(bx, tx), ey = __fsub_rn(by, ty);
+            const float len = __fsqrt_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)));
+            cur = __fadd_rn(cur, len);
+            if (cur > d) {
+                const float ny = __fdiv_rn(ey, len);
+                do {
+                    const float delta = __fsub_rn(cur, d);
+                    put(t, __fadd_rn(ty, __fmul_rn(ny, delta)), k0 + i, i);
+                    ++t;
+                    d = dist_of(t);
+                } while (t < q.N && cur > d);
+            }
+            bx = tx; by = ty;
+        }
+        if (t < q.N) {
+            const float ly = vy(k0 + n - 1);
+            for (; t < q.N; ++t) put(t, ly, k0 + n - 1, n - 1);
+        }
+    }
+    x0[b] = T(0); x0[q.stride + b] = T(0);
+}
+
 struct PlantParams {
     long long count, stride;
     double a22, a23, a32, a33, b2, b3, Tv, Tv_l;
@@ -151,6 +222,7 @@ int bmpc_cl_init(bmpc_t* h, int64_t count, const bmpc_cl_config* cfg, const doub
     int rc = bmpc_reset(h);                                 // fresh controllers: controls = 0, targets = 0, v = 0
     if (rc) return rc;
     h->full_targets = false;                                // the loop uses set_target(val): one target for all steps
+    h->cl_horizon = false;                                  // ... unless bmpc_cl_set_horizon_targets asks for one per step
     h->cl_cfg = *cfg; h->cl_count = count;
     const size_t np = (size_t)cfg->npath, cap = (size_t)h->cap;
     BMPC_CUDA(h->cl_path.reserve(4 * np * 8));
@@ -179,6 +251,26 @@ int bmpc_cl_init(bmpc_t* h, int64_t count, const bmpc_cl_config* cfg, const doub
     return BMPC_OK;
 }
 
+int bmpc_cl_set_horizon_targets(bmpc_t* h, int enable, double d0, double step)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_cl_set_horizon_targets: null handle");
+    if (!h->cl_ready) return fail(BMPC_E_STATE, "bmpc_cl_set_horizon_targets: bmpc_cl_init has not been called");
+    if (enable && !((float)step >= 0.0f && std::isfinite(d0))) return fail(BMPC_E_INVALID, "bmpc_cl_set_horizon_targets: need a finite d0 and step >= 0");
+    BMPC_CUDA(cudaSetDevice(h->device));
+    if (enable) {
+        // every tick rewrites all N steps of every vehicle, so the ring only has to exist
+        const size_t bytes = (size_t)h->cap * h->S * h->elem * h->N;
+        BMPC_CUDA(h->target_full.reserve(bytes));
+        BMPC_CUDA(cudaMemsetAsync(h->target_full.p, 0, bytes, h->stream));
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));
+        h->head = 0;
+    }
+    h->full_targets = enable != 0;
+    h->cl_horizon = enable != 0;
+    h->cl_h_d0 = (float)d0; h->cl_h_step = (float)step;
+    return BMPC_OK;
+}
+
 int bmpc_cl_run(bmpc_t* h, int ticks)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_cl_run: null handle");
@@ -190,13 +282,17 @@ int bmpc_cl_run(bmpc_t* h, int ticks)
     const double* path = (const double*)h->cl_path.p;
     ClParams cp{count, h->cap, h->cl_cfg.P, h->cl_cfg.npath, (float)h->cl_cfg.lookahead, (float)h->cl_cfg.v,
                 path, path + np, path + 2 * np, path + 3 * np, (const double*)h->cl_pose.p, (double*)h->cl_tgt.p,
-                (int32_t*)h->cl_idx.p};
+                (int32_t*)h->cl_idx.p, h->N, 0, h->cl_h_d0, h->cl_h_step};
     const double Tv = h->cl_cfg.T * h->cl_cfg.v;
     PlantParams pp{count, h->cap, h->hA[10], h->hA[11], h->hA[14], h->hA[15], h->hB[2], h->hB[3], Tv, Tv / h->cl_cfg.l,
                    (double*)h->cl_pose.p, (const uint32_t*)h->iters.p, (unsigned long long*)h->cl_itot.p, (uint32_t*)h->cl_imax.p};
     const unsigned grid = (unsigned)((count + 127) / 128);
     for (int t = 0; t < ticks; ++t) {
-        if (h->elem == 8) k_cl_prepare<double><<<grid, 128, 0, h->stream>>>(cp, (double*)h->x0.p, (double*)h->target_const.p);
+        if (h->cl_horizon) {
+            cp.head = h->head;                              // the ring's step-0 slot moves by one per warm solve (mpc.h:236-237)
+            if (h->elem == 8) k_cl_prepare_horizon<double><<<grid, 128, 0, h->stream>>>(cp, (double*)h->x0.p, (double*)h->target_full.p);
+            else k_cl_prepare_horizon<float><<<grid, 128, 0, h->stream>>>(cp, (float*)h->x0.p, (float*)h->target_full.p);
+        } else if (h->elem == 8) k_cl_prepare<double><<<grid, 128, 0, h->stream>>>(cp, (double*)h->x0.p, (double*)h->target_const.p);
         else k_cl_prepare<float><<<grid, 128, 0, h->stream>>>(cp, (float*)h->x0.p, (float*)h->target_const.p);
         BMPC_CUDA(cudaGetLastError());
         h->launches++;

@@ -126,6 +126,82 @@ __global__ void k_extract(long long count, int P, const int32_t* __restrict__ np
     idx[b] = ri; flag[b] = rf; opx[b] = rx; opy[b] = ry; odx[b] = rdx; ody[b] = rdy; ovel[b] = rv;
 }
 
+// getTrajectoryPoint for `steps` ascending look-ahead distances d_t = d0 + t*step of the same polyline in ONE sequential
+// scan (a target per horizon step).  The arc length `cur` is the same float sum whatever the
+// distance asked for, so step t's point is produced by the first segment with cur > d_t — exactly what k_extract
+// returns for d_t; several steps may fall into one segment, the remaining ones get the last point (:439-442).
+// Outputs are instance-major [count][steps] (the host layout): a thread collects its `steps` results in its row of a
+// shared-memory tile (row stride steps|1 words: conflict-free), then the block writes its contiguous slice of each
+// output array with coalesced stores.
+__global__ void k_extract_horizon(long long count, int P, const int32_t* __restrict__ npoints, const float* __restrict__ px,
+                                  const float* __restrict__ py, const float* __restrict__ dx, const float* __restrict__ dy,
+                                  const float* __restrict__ vel, long long si, long long sp, const float* __restrict__ d0,
+                                  const float* __restrict__ step, int steps, int32_t* __restrict__ idx,
+                                  uint8_t* __restrict__ flag, float* __restrict__ opx, float* __restrict__ opy,
+                                  float* __restrict__ odx, float* __restrict__ ody, float* __restrict__ ovel)
+{
+    extern __shared__ __align__(16) unsigned char hz_raw[];
+    const int rs = steps | 1;                                        // row stride in words
+    const int tile = blockDim.x * rs;
+    float* sm = reinterpret_cast<float*>(hz_raw);                     // 5 float planes, then the idx plane, then flags
+    int32_t* sm_i = reinterpret_cast<int32_t*>(sm + 5 * tile);
+    uint8_t* sm_f = reinterpret_cast<uint8_t*>(sm_i + tile);
+    const long long b0 = (long long)blockIdx.x * blockDim.x, b = b0 + threadIdx.x;
+    const int row = threadIdx.x * rs;
+    auto emit = [&](int t, int i, uint8_t f, float x, float y, float ddx, float ddy, float v) {
+        sm[row + t] = x; sm[tile + row + t] = y; sm[2 * tile + row + t] = ddx; sm[3 * tile + row + t] = ddy;
+        sm[4 * tile + row + t] = v; sm_i[row + t] = i; sm_f[row + t] = f;
+    };
+    if (b < count) {
+        const float d_0 = d0[b], st = step[b];
+        int n = npoints ? npoints[b] : P;
+        if (n > P) n = P;
+        const long long o = b * si;
+        auto dist_of = [&](int t) { return __fadd_rn(d_0, __fmul_rn((float)t, st)); };
+        int t = 0;
+        if (n <= 0) {                                                // :394-407 for every step
+            for (; t < steps; ++t) emit(t, -1, BMPC_PT_EMPTY, dist_of(t), 0.0f, 1.0f, 0.0f, 0.0f);
+        } else {
+            float cur = 0.0f;                                        // :423
+            float bx = px[o], by = py[o];
+            float d = dist_of(0);
+            for (int i = 1; i < n && t < steps; ++i) {               // :424
+                const float tx = px[o + i * sp], ty = py[o + i * sp];
+                const float ex = __fsub_rn(bx, tx), ey = __fsub_rn(by, ty);
+                const float len = __fsqrt_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)));   // :427
+                cur = __fadd_rn(cur, len);
+                if (cur > d) {                                       // :428 strict
+                    const float nx = __fdiv_rn(ex, len), ny = __fdiv_rn(ey, len);                // :432
+                    const float ddx = dx[o + i * sp], ddy = dy[o + i * sp], v = vel[o + i * sp];
+                    do {
+                        const float delta = __fsub_rn(cur, d);      // :431
+                        emit(t, i, BMPC_PT_INTERPOLATED, __fadd_rn(tx, __fmul_rn(nx, delta)), __fadd_rn(ty, __fmul_rn(ny, delta)), ddx, ddy, v);
+                        ++t;
+                        d = dist_of(t);
+                    } while (t < steps && cur > d);
+                }
+                bx = tx; by = ty;
+            }
+            if (t < steps) {                                         // :439-442
+                const long long l = o + (long long)(n - 1) * sp;
+                const float x = px[l], y = py[l], ddx = dx[l], ddy = dy[l], v = vel[l];
+                for (; t < steps; ++t) emit(t, n - 1, BMPC_PT_LAST, x, y, ddx, ddy, v);
+            }
+        }
+    }
+    __syncthreads();
+    const long long rows = count - b0 < blockDim.x ? count - b0 : blockDim.x;
+    const long long total = rows * steps, base = b0 * steps;
+    float* const outs[5] = {opx, opy, odx, ody, ovel};
+    for (long long e = threadIdx.x; e < total; e += blockDim.x) {
+        const int at = (int)(e / steps) * rs + (int)(e % steps);
+#pragma unroll
+        for (int a = 0; a < 5; ++a) outs[a][base + e] = sm[a * tile + at];
+        idx[base + e] = sm_i[at];
+        flag[base + e] = sm_f[at];
+    }
+}
+
 inline unsigned blocks_for(long long count, int block) { return (unsigned)((count + block - 1) / block); }
 }  // namespace
 
@@ -181,6 +257,24 @@ cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const
     if (count <= 0) return cudaSuccess;
     k_extract<<<blocks_for(count, 128), 128, 0, st>>>(count, P, npoints, px, py, dx, dy, vel, stride_instance,
                                                      stride_point, dist, idx, flag, opx, opy, odx, ody, ovel);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_extract_horizon(long long count, int P, const int32_t* npoints, const float* px, const float* py,
+                                   const float* dx, const float* dy, const float* vel, long long stride_instance,
+                                   long long stride_point, const float* d0, const float* step, int steps, int32_t* idx,
+                                   uint8_t* flag, float* opx, float* opy, float* odx, float* ody, float* ovel, cudaStream_t st)
+{
+    if (count <= 0 || steps <= 0) return cudaSuccess;
+    // 25 bytes per (thread, step) of shared-memory tile; the block shrinks for long horizons
+    int block = 128;
+    auto bytes = [&](int blk) { return (size_t)blk * (steps | 1) * 25 + 16; };
+    while (block > 32 && bytes(block) > 96 * 1024) block >>= 1;
+    if (bytes(block) > 227 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(k_extract_horizon, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    k_extract_horizon<<<blocks_for(count, block), block, bytes(block), st>>>(count, P, npoints, px, py, dx, dy, vel, stride_instance,
+                                                                            stride_point, d0, step, steps, idx, flag, opx, opy, odx, ody, ovel);
     return cudaGetLastError();
 }
 

@@ -80,6 +80,9 @@ SIGNATURES = {
                             [C.c_int64, C.c_int64, _dp, _dp, _fp, _fp, _i32p, _u8p]),
     "bmpc_cl_init": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p] + [_dp] * 6),
     "bmpc_cl_run": (C.c_int, [C.c_void_p, C.c_int]),
+    "bmpc_cl_set_horizon_targets": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double]),
+    "bmpc_extract_horizon": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _fp, C.c_int,
+                                       _i32p, _u8p] + [_fp] * 5),
     "bmpc_cl_get": (C.c_int, [C.c_void_p, C.c_int64, _dp, _dp, _dp, _dp, _i32p, C.POINTER(C.c_uint64), _u32p]),
     "bmpc_group_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,
                                     C.POINTER(C.c_int), C.c_int, C.c_int]),
@@ -367,6 +370,12 @@ class BatchedMPC:
         _check(lib().bmpc_cl_init(self._h, pose0.shape[0], C.byref(cfg), _p(px), _p(py), _p(tx), _p(ty), _p(pose0), _p(a0)))
         self._cl_count = pose0.shape[0]
 
+    def cl_set_horizon_targets(self, enable: bool = True, d0: float | None = None, step: float | None = None, v=1.0, T=0.1):
+        """A target per horizon step, sampled at d_t = d0 + t*step (defaults d0 = step = T*v); see include/bmpc.h."""
+        d0 = T * v if d0 is None else d0
+        step = T * v if step is None else step
+        _check(lib().bmpc_cl_set_horizon_targets(self._h, int(enable), d0, step))
+
     def cl_run(self, ticks: int):
         _check(lib().bmpc_cl_run(self._h, ticks))
 
@@ -459,6 +468,19 @@ class BatchedMPC:
         _check(lib().bmpc_fleet_put_pid(self._h, which, i.shape[0], _p(i, _fp), _p(p, _fp), _p(f, _u8p)))
 
     # ---- trajectory point ---------------------------------------------------------------------------------------------------
+    def extract_horizon(self, px, py, dx, dy, vel, d0, step, steps: int, npoints=None, layout: str = "shared"):
+        """getTrajectoryPoint at d_t = d0 + t*step, t < steps, per instance: (idx[B][steps], flag, (px, py, dx, dy, vel))."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+        d0 = np.ascontiguousarray(d0, dtype=np.float32); step = np.ascontiguousarray(step, dtype=np.float32)
+        B = d0.shape[0]
+        P, si, sp = self._poly_strides(arrs[0], layout, B)
+        npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+        idx = np.empty((B, steps), dtype=np.int32); flag = np.empty((B, steps), dtype=np.uint8)
+        outs = [np.empty((B, steps), dtype=np.float32) for _ in range(5)]
+        _check(lib().bmpc_extract_horizon(self._h, B, P, _p(npts, _i32p), *[_p(a, _fp) for a in arrs], si, sp, _p(d0, _fp),
+                                          _p(step, _fp), steps, _p(idx, _i32p), _p(flag, _u8p), *[_p(o, _fp) for o in outs]))
+        return idx, flag, tuple(outs)
+
     def extract_points(self, px, py, dx, dy, vel, dist, npoints=None, layout: str = "shared"):
         """getTrajectoryPoint for a batch.  layout 'shared': arrays [P] (one polyline for all); 'pb': [P][B]
         point-major (coalesced on the device); 'bp': [B][P].  Returns (idx, flag, (px, py, dx, dy, vel))."""
