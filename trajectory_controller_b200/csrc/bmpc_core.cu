@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -222,6 +223,20 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(h->pg_list.alloc_zero(h->pg_ring * 4, h->stream), "alloc pg_list");
     chk(h->park.reserve(h->pg_ring * 3 * h->NI * es), "alloc park");
     chk(h->park_iter.reserve(h->pg_ring * 4), "alloc park_iter");
+    // Stage C (pair_kernel.cuh): 16 instances per warp; one warp per SM sub-partition is the fast configuration, so stage B
+    // hands over when that many instances are left and batches up to twice that go to stage C directly.
+    // BMPC_PAIR_THRESHOLD / BMPC_PAIR_DIRECT: developer overrides for A/B measurements.
+    h->pair_threshold = (long long)h->sm_count * 4 * 16;
+    h->pair_direct_max = 2 * h->pair_threshold;
+    if (const char* e = std::getenv("BMPC_PAIR_THRESHOLD")) h->pair_threshold = std::atoll(e);
+    if (const char* e = std::getenv("BMPC_PAIR_DIRECT")) h->pair_direct_max = std::atoll(e);
+    if (h->pair_threshold < 0) h->pair_threshold = 0;
+    if (ops->S == 4 && ops->I == 1 && h->pair_threshold > 0) {
+        const size_t ct = (size_t)h->pair_threshold;
+        chk(h->c_list.reserve(ct * 4), "alloc c_list");
+        chk(h->c_park.reserve(ct * 3 * h->NI * es), "alloc c_park");
+        chk(h->c_iter.reserve(ct * 4), "alloc c_iter");
+    }
     chk(h->small.alloc_zero(8 * 4096, h->stream), "alloc small");
     h->pinned_bytes = 8 * 4096;
     chk(cudaHostAlloc(&h->pinned, h->pinned_bytes, cudaHostAllocDefault), "cudaHostAlloc");
@@ -238,7 +253,7 @@ void bmpc_destroy(bmpc_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
                       &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
-                      &h->pg_list, &h->park, &h->park_iter, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
+                      &h->pg_list, &h->park, &h->park_iter, &h->c_list, &h->c_park, &h->c_iter, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
     for (DevBuf* b : bufs) b->release();
     for (DevBuf& b : h->ex) b.release();
     for (DevBuf& b : h->lut) b.release();
@@ -271,12 +286,13 @@ int bmpc_set_split(bmpc_t* h, int enable)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_set_split: null handle");
     h->split = enable != 0;
-    if (enable >= 8) {   // developer A/B: 8 | 1 (fairness slices) | 2 (retirement of surplus warps) | 4 (symmetric-bound kernel)
-        h->slice = (enable & 1) != 0; h->retire = (enable & 2) != 0; h->sym = (enable & 4) != 0;
+    if (enable >= 8) {   // developer A/B: 8 | 1 (fairness slices) | 2 (retirement of surplus warps) | 4 (symmetric-bound kernel) | 16 (stage C)
+        h->slice = (enable & 1) != 0; h->retire = (enable & 2) != 0; h->sym = (enable & 4) != 0; h->pair = (enable & 16) != 0;
     } else {
         h->slice = enable != 2;
         h->retire = enable != 2;
         h->sym = enable != 3;
+        h->pair = enable == 1;
     }
     return BMPC_OK;
 }

@@ -96,6 +96,10 @@ struct bmpc_handle {
     bool retire = true;              // stage B may retire surplus warps near the end of a launch (bmpc_set_split(h, 2) turns it off)
     bool sym = true;                 // stage B may use its symmetric-bound kernel (bmpc_set_split(h, 3) turns it off)
     bool split = true;               // bmpc_set_split; the two-stage solve is used whenever the shape offers it
+    bool pair = true;                // stage C (pair_kernel.cuh) may be used: tails, small batches, per-instance models, long horizons
+    long long pair_threshold = 0;    // stage B hands over to stage C once this many instances or fewer are unfinished
+    long long pair_direct_max = 0;   // batches up to this size skip stage B
+    bmpc::DevBuf c_list, c_park, c_iter;   // stage C's list (by-slot rows of stride pair_threshold)
     bool full_targets = false;
     int head = 0;
 

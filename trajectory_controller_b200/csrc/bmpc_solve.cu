@@ -202,6 +202,19 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
         BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, 0, &kp0));
         g.sym = kp0.sym_ok;
     }
+    // Stage C (pair_kernel.cuh): one instance per lane pair.  Same preconditions as the symmetric-bound kernel (the model
+    // check of bmpc_set_model; stage A keeps non-finite instances to itself when g.sym is set).  It replaces stage B
+    // where the per-lane layout is slow or the batch is small — per-instance models (model block in shared memory),
+    // horizons whose u / MM do not fit a lane's registers, batches up to pair_direct_max — and takes over the last
+    // pair_threshold instances of every other launch.
+    const bool pair_ok = split && h->pair && h->sym && h->sym_ok && h->solve_ops->has_pair && h->c_list.p != nullptr;
+    const bool lane_regs = (long long)h->NI * h->elem <= 256;          // PgLayout::UREG: stage B runs from registers
+    const bool pair_direct = pair_ok && (count <= h->pair_direct_max || h->per_instance || !lane_regs);
+    const bool pair_tail = pair_ok && !pair_direct && g.sym && h->pair_threshold > 0;
+    if (pair_direct) g.sym = 1;
+    g.c_direct = pair_direct; g.c_threshold = pair_tail ? (unsigned)h->pair_threshold : 0u;
+    g.c_list = (uint32_t*)h->c_list.p; g.c_park = h->c_park.p; g.c_iter = (uint32_t*)h->c_iter.p;
+    g.c_stride = (unsigned)h->pair_threshold;
     g.pg_mask = (unsigned)(h->pg_ring - 1);
     g.park = h->park.p; g.park_iter = (uint32_t*)h->park_iter.p;
     // Stage-B scheduling (pg_kernel.cuh).  Slot reuse (parking) is what retirement and fairness slices need; it costs a
@@ -214,6 +227,7 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     // retirement needs more than one warp per SM sub-partition's worth of instances to have anything to retire
     const bool retire = h->retire && small_enough && count > 1ll * h->sm_count * 128;
     g.pg_reuse = (g.pg_slice || retire) ? (1 | (retire ? 2 : 0)) : 0;   // bit 0: parking, bit 1: retirement
+    if (pair_direct) { g.pg_slice = 0; g.pg_reuse = 0; }                // stage B does not run: stage A's ring entries stay behind
     // A launch that recycles ring slots needs every slot empty at the start and leaves it so; one that does not leaves
     // stage A's entries behind.  So the ring is wiped only when a recycling launch follows a non-recycling one.
     if (split && g.pg_reuse && h->ring_dirty) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
@@ -237,11 +251,21 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     h->timed_split = split;
     if (split) {
         BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
-        KernelInfo kp;
-        BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, g.sym, &kp));
-        g.warp_limit_b = limit_for(kp.warps);
-        BMPC_CUDA(h->solve_ops->pg(h->precision, h->mode, h->per_instance, g, grid, h->stream));
-        h->launches++;
+        if (!pair_direct) {
+            KernelInfo kp;
+            BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, g.sym, &kp));
+            g.warp_limit_b = limit_for(kp.warps);
+            BMPC_CUDA(h->solve_ops->pg(h->precision, h->mode, h->per_instance, g, grid, h->stream));
+            h->launches++;
+        }
+        if (pair_direct || pair_tail) {
+            // 16 instances per warp; the kernel itself lets only as many warps per CTA work as its list needs
+            const long long most = pair_direct ? count : (count < h->pair_threshold ? count : h->pair_threshold);
+            const long long pw = (most + 15) / 16;
+            const int grid_c = (int)(pw < h->sm_count ? pw : h->sm_count);
+            BMPC_CUDA(h->solve_ops->pair(h->precision, h->mode, h->per_instance, g, grid_c, h->stream));
+            h->launches++;
+        }
     }
     BMPC_CUDA(cudaEventRecord(h->ev1, h->stream));
     h->timed = true;

@@ -25,6 +25,8 @@ struct GenericSolve {
     int pg_reuse;                                // stage B recycles ring slots (parking enabled)
     int sym;                                     // bounds are symmetric and the model is tame: stage B may run its SYM kernel
     int warp_limit_a, warp_limit_b;              // warps per CTA that take work in stage A / stage B
+    // stage C (pair_kernel.cuh)
+    int c_direct; unsigned c_threshold; uint32_t* c_list; void* c_park; uint32_t* c_iter; unsigned c_stride;
 };
 
 // mpc.h:114-123 for `count` models held SoA [elem][stride] on the device.
@@ -48,6 +50,10 @@ struct ShapeOps {
     int has_pg;
     cudaError_t (*pg)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
     cudaError_t (*pg_info)(int precision, int mode, int pim, int sym, KernelInfo* out);
+    // stage C: one instance per lane pair (bicycle4 pattern, even horizons); has_pair == 0 elsewhere
+    int has_pair;
+    cudaError_t (*pair)(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st);
+    cudaError_t (*pair_info)(int precision, int mode, int pim, KernelInfo* out);
 };
 
 }  // namespace bmpc

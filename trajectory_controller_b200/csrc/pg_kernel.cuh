@@ -472,6 +472,7 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         if (!__any_sync(FULL, st == kActive)) {
             if (!__any_sync(FULL, st == kWait)) break;             // no ticket of this warp is still open
             if (q[3] == 0) break;                                  // every instance of the launch has finished
+            if (p.c_threshold != 0 && q[3] == q[6]) break;         // ... or waits in stage C's list (nothing is active or parked here)
             if (q[4] != 0) break;                                  // another warp gave up (ring overrun)
             __nanosleep(500); since = 0;
             continue;
@@ -526,6 +527,36 @@ pg_kernel(const __grid_constant__ SolveParams<T, S, I, N> p)
         }
         const unsigned finmask = __ballot_sync(FULL, fin);
         if (finmask && lane == (__ffs(finmask) - 1)) atomicAdd(p.queue + 3, 0ull - (unsigned long long)__popc(finmask));
+
+        // ---------------- hand-over to stage C (pair_kernel.cuh): once p.c_threshold or fewer instances are unfinished, the
+        // launch is bound by the latency of its longest solves, which the lane-pair kernel halves.  Every warp parks its
+        // live instances in stage C's list (by-slot rows like the ring's, tail = queue[6]); instances that open tickets
+        // still bring are forwarded the same way after their next passes.  `unfinished` only falls, so the decision
+        // is taken once and for all by every warp on its own.
+        if (p.c_threshold != 0 && (unsigned)q[3] <= p.c_threshold) {
+            const unsigned actmask = __ballot_sync(FULL, st == kActive);
+            if (actmask) {
+                const int leader = __ffs(actmask) - 1;
+                unsigned long long pos = 0;
+                if (lane == leader) pos = atomicAdd(p.queue + 6, (unsigned long long)__popc(actmask));
+                pos = __shfl_sync(FULL, pos, leader);
+                if (st == kActive) {
+                    const unsigned ps = (unsigned)pos + (unsigned)__popc(actmask & ((1u << lane) - 1u));
+                    T* dst = p.c_park + ps;
+                    const long long cs = (long long)p.c_stride;
+#pragma unroll(L::UNR_K)
+                    for (int k = 0; k < NI; ++k) {
+                        dst[(long long)k * cs] = sv.getU(k);
+                        dst[(long long)(NI + k) * cs] = sv.getV(k);
+                        dst[(long long)(2 * NI + k) * cs] = sv.getMM(k);
+                    }
+                    p.c_iter[ps] = aux;
+                    p.c_list[ps] = get_inst();
+                    st = kNeed;
+                }
+            }
+            continue;
+        }
 
         // ---------------- scheduling decisions (see the kernel comment)
         if (reuse) {

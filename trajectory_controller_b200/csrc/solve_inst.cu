@@ -5,6 +5,7 @@
 #include "ctor_kernel.cuh"
 #include "dispatch.h"
 #include "patterns.h"
+#include "pair_kernel.cuh"
 #include "pg_kernel.cuh"
 #include "solve_kernel.cuh"
 
@@ -43,6 +44,8 @@ void fill_params(SolveParams<T, S_, I_, N_>& p, const GenericSolve& g)
     p.queue = g.queue;
     p.split = g.split; p.pg_list = g.pg_list; p.pg_mask = g.pg_mask; p.pg_slice = g.pg_slice;
     p.park = (T*)g.park; p.park_iter = g.park_iter; p.pg_reuse = g.pg_reuse; p.sym = g.sym;
+    p.c_direct = g.c_direct; p.c_threshold = g.c_threshold; p.c_list = g.c_list; p.c_park = (T*)g.c_park; p.c_iter = g.c_iter;
+    p.c_stride = g.c_stride;
 }
 
 template <typename T, bool EXACT, bool PIM>
@@ -118,6 +121,41 @@ cudaError_t info_pg(int sym, KernelInfo* out)
     }
 }
 
+// stage C: the lane-pair kernel exists for the block-triangular (4,1) pattern and even horizons
+constexpr bool kHasPair = (S_ == 4 && I_ == 1 && N_ % 2 == 0 && PAT_::ANZ == 0xCC63u && PAT_::AONE == 0x0421u && PAT_::BNZ == 0x8u &&
+                           PAT_::BONE == 0u && PAT_::CNZ == 0u && PAT_::QNZ == 0x3u);
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t launch_pair(const GenericSolve& g, int grid, cudaStream_t st)
+{
+    if constexpr (!kHasPair) return cudaErrorNotSupported;
+    else {
+        using L = PairLayout<T, N_, PIM>;
+        SolveParams<T, S_, I_, N_> p;
+        fill_params<T, PIM>(p, g);
+        auto kern = pair_kernel<T, N_, EXACT, PIM>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(p);
+        return cudaGetLastError();
+    }
+}
+
+template <typename T, bool EXACT, bool PIM>
+cudaError_t info_pair(KernelInfo* out)
+{
+    if constexpr (!kHasPair) return cudaErrorNotSupported;
+    else {
+        using L = PairLayout<T, N_, PIM>;
+        cudaFuncAttributes a;
+        cudaError_t e = cudaFuncGetAttributes(&a, pair_kernel<T, N_, EXACT, PIM>);
+        if (e != cudaSuccess) return e;
+        out->block = L::THREADS; out->smem_bytes = L::SMEM_BYTES; out->regs = a.numRegs; out->warps = L::WARPS;
+        out->local_bytes = (int)a.localSizeBytes; out->sym_ok = 1;
+        return cudaSuccess;
+    }
+}
+
 template <typename T, bool EXACT>
 cudaError_t launch_ctor(const GenericCtor& g, cudaStream_t st)
 {
@@ -149,6 +187,10 @@ cudaError_t pg_entry(int precision, int mode, int pim, const GenericSolve& g, in
 { BMPC_DISPATCH(launch_pg, g, grid, st); }
 cudaError_t pg_info_entry(int precision, int mode, int pim, int sym, KernelInfo* out)
 { BMPC_DISPATCH(info_pg, sym, out); }
+cudaError_t pair_entry(int precision, int mode, int pim, const GenericSolve& g, int grid, cudaStream_t st)
+{ BMPC_DISPATCH(launch_pair, g, grid, st); }
+cudaError_t pair_info_entry(int precision, int mode, int pim, KernelInfo* out)
+{ BMPC_DISPATCH(info_pair, out); }
 template <bool DENSE>
 cudaError_t ctor_entry_t(int precision, int mode, const GenericCtor& g, cudaStream_t st)
 {
@@ -169,6 +211,6 @@ cudaError_t ctor_entry(int precision, int mode, const GenericCtor& g, cudaStream
 extern const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT);
 const ShapeOps BMPC_CAT(BMPC_S, BMPC_I, BMPC_N, BMPC_PAT) = {
     S_, I_, N_, BMPC_STR(BMPC_PAT), PAT_::ANZ, PAT_::AONE, PAT_::BNZ, PAT_::BONE, PAT_::CNZ, PAT_::QNZ,
-    solve_entry, ctor_entry, info_entry, kHasPg ? 1 : 0, pg_entry, pg_info_entry};
+    solve_entry, ctor_entry, info_entry, kHasPg ? 1 : 0, pg_entry, pg_info_entry, kHasPair ? 1 : 0, pair_entry, pair_info_entry};
 
 }  // namespace bmpc

@@ -65,7 +65,7 @@ struct SolveParams {
     // per-instance models, SoA [elem][stride]
     const T *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;
     unsigned long long* queue;   // [0] next unclaimed instance; [1] ring tail; [2] ring head; [3] instances stage B has
-                                 // not finished; [4] error word (ring overrun)
+                                 // not finished; [4] error word (ring overrun); [6] stage-C list length; [7] stage-C tickets
     // split solve (pg_kernel.cuh): stage A parks an instance that reaches iter == 50 in a slot of the hand-over ring
     int split;
     uint32_t* pg_list;   // ring of instance ids, capacity pg_mask + 1 (a power of two), 0xffffffff = empty
@@ -76,6 +76,15 @@ struct SolveParams {
     int pg_slice;        // stage B may time-slice small batches (pg_kernel.cuh)
     int pg_reuse;        // stage B recycles ring slots (parking enabled)
     int sym;             // stage B runs the symmetric-bound kernel: instances whose linear term is not finite stay in stage A
+    // stage C (pair_kernel.cuh): one instance per lane pair.  c_direct: stage B is skipped, stage C consumes stage A's
+    // hand-over ring [0, queue[1]); else stage B parks its last c_threshold instances in c_list / c_park / c_iter
+    // (by-slot rows of stride c_stride, tail in queue[6]) and stage C consumes those.  queue[7] = stage C's tickets.
+    int c_direct;
+    unsigned c_threshold;   // stage B hands over once this many instances or fewer are unfinished (0 = never)
+    uint32_t* c_list;
+    T* c_park;
+    uint32_t* c_iter;
+    unsigned c_stride;
 };
 
 __host__ __device__ constexpr int popc_c(unsigned x) { int n = 0; while (x) { n += int(x & 1u); x >>= 1; } return n; }
