@@ -224,10 +224,10 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(h->park.reserve(h->pg_ring * 3 * h->NI * es), "alloc park");
     chk(h->park_iter.reserve(h->pg_ring * 4), "alloc park_iter");
     // Stage C (pair_kernel.cuh): 16 instances per warp; one warp per SM sub-partition is the fast configuration, so stage B
-    // hands over when that many instances are left and batches up to twice that go to stage C directly.
+    // hands over when that many instances are left and batches up to that size go to stage C directly.
     // BMPC_PAIR_THRESHOLD / BMPC_PAIR_DIRECT: developer overrides for A/B measurements.
     h->pair_threshold = (long long)h->sm_count * 4 * 16;
-    h->pair_direct_max = 2 * h->pair_threshold;
+    h->pair_direct_max = h->pair_threshold;
     if (const char* e = std::getenv("BMPC_PAIR_THRESHOLD")) h->pair_threshold = std::atoll(e);
     if (const char* e = std::getenv("BMPC_PAIR_DIRECT")) h->pair_direct_max = std::atoll(e);
     if (h->pair_threshold < 0) h->pair_threshold = 0;

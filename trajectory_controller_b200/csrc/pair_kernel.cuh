@@ -52,8 +52,8 @@ struct PairLayout {
     static constexpr bool MMREG = (2 * NH * WORDS <= 128);
     // shared memory per lane, in elements: N pair slots (H: the Q*M stash of the forward sweep, slot s = horizon step s;
     // both lanes: (u_old, v_old) of the lane's own entry e in slot e once the backward sweep has consumed it), v, MM
-    static constexpr int O_Q = 0;
-    static constexpr int O_V = 2 * N;
+    static constexpr int O_Q = 0;                          // slot s lives at pair index s + 1: one pad slot in front
+    static constexpr int O_V = 2 * (N + 1);
     static constexpr int O_MM = O_V + NH;
     static constexpr int ELEMS = O_MM + (MMREG ? 0 : NH);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
@@ -78,13 +78,14 @@ struct PairSolver {
     T h1, mc, g1, g2;                // backward
     T b3, R, hi, inv_lambda, beta, eps;
     bool isH;
-    unsigned a1, a2, a2own;          // shared-window byte addresses: single elements / pair slots / pair slot of entry (0 + role)
+    unsigned a1, a2, a2own, a2lag;   // shared-window byte addresses: single elements / pair slots / slot + role (own entries) / slot + (L ? 1 : 0)
     T u[NH];
     T mm[L::MMREG ? NH : 1];
     unsigned long long sat;          // bit j set <=> |u[j]| == hi (entry sits on a bound), own entries
 
-    __device__ __forceinline__ unsigned pair_addr(int slot) const { return a2 + (unsigned)(2 * slot * 32 * ES); }
-    __device__ __forceinline__ unsigned own_addr(int j) const { return a2own + (unsigned)(4 * j * 32 * ES); }   // slot 2j + role
+    __device__ __forceinline__ unsigned pair_addr(int slot) const { return a2 + (unsigned)(2 * (slot + 1) * 32 * ES); }
+    __device__ __forceinline__ unsigned own_addr(int j) const { return a2own + (unsigned)(2 * (2 * j + 1) * 32 * ES); }   // slot 2j + role
+    __device__ __forceinline__ unsigned lag_addr(int slot) const { return a2lag + (unsigned)(2 * (slot + 1) * 32 * ES); }  // slot + 1 on L
     __device__ __forceinline__ unsigned elem_addr(int e) const { return a1 + (unsigned)(e * 32 * ES); }
     __device__ __forceinline__ T getV(int j) const { return IO::ld1(elem_addr(L::O_V + j)); }
     __device__ __forceinline__ void setV(int j, T v) { IO::st1(elem_addr(L::O_V + j), v); }
@@ -102,9 +103,10 @@ struct PairSolver {
         c1 = high ? T(0) : a32; c2 = high ? T(1) : a33; c3 = high ? a12 : b3_;
         qP = high ? q0 : T(0); qQ = high ? q1 : T(0);                       // mpc.h:279, H only (L's products are unused zeros)
         // backward (mpc.h:281), state (p, q) = (w2, w3) on L, (w0, w1) on H, X = the partner's q of the previous step:
-        //   p' = (h1*X + p) + mc*mv                     L: (a12*w1 + w2) + a32*w3       H: (0*w3 + w0) + 1*stash0
-        //   q' = stash1 + (g1*p + g2*q)                 L: -0 + (a23*w2 + a33*w3)       H: stash1 + (a01*w0 + 1*w1)
-        h1 = high ? T(0) : a12; mc = high ? T(1) : a32;
+        //   p' = ((h1*X + p) + stash0) + mc*q           L: ((a12*w1 + w2) + 0) + a32*w3   H: ((0*w3 + w0) + stash0) + 0*w1
+        //   q' = stash1 + (g1*p + g2*q)                 L: 0 + (a23*w2 + a33*w3)          H: stash1 + (a01*w0 + 1*w1)
+        // (L's pair slots hold the zeros its forward sweep stored)
+        h1 = high ? T(0) : a12; mc = high ? T(0) : a32;
         g1 = high ? a01 : a23; g2 = high ? T(1) : a33;
         b3 = b3_; R = r; hi = hi_; eps = eps_;
         inv_lambda = A_::div(T(1), lambda);                                                      // mpc.h:342
@@ -124,72 +126,103 @@ struct PairSolver {
 
     // One projected-gradient iteration of the pair's instance.  Returns true when the reference would NOT break at
     // mpc.h:310 (the update stands); the value is the same on both lanes.
+    //
+    // Schedule.  A warp issues in order, so a shuffle whose result is consumed in the next horizon step would stall the
+    // whole pair for its latency.  The lane that CONSUMES the crossing value therefore runs one horizon step behind the
+    // lane that produces it: every exchange issued at the end of trip j is first read in trip j+2.
+    //   forward  trip k = 0..N  : L computes step k (k < N), H computes step k-1 (k >= 1) from L's m2 of step k-2
+    //   backward trip k = 0..N+1: H computes step N-1-k (k < N), L computes step N-k (1 <= k <= N) from H's w1 of step
+    //                             N-k+1; at odd k >= 3 both lanes test and update one control entry: H its entry N+2-k
+    //                             (w3 received two trips ago), L its entry N+1-k (w3 = its own q of the trip before)
     __device__ __forceinline__ bool pass()
     {
         // ---------------- forward sweep: M[i] = A*M[i-1] + B*u[i] (mpc.h:275-277), Q-scaling and stash (mpc.h:279)
+        T r_old = xchg(isH ? u[0] : T(0));                            // L: control entry 1;  H: "m2 of step -1" = 0
         T pcur = T(0);
-        T qcur = A_::mul(c3, isH ? T(0) : u[0]);                      // step 0: M[0] = B*u[0]: m3 = b3*u0, the rest zero
+        T qcur = A_::mul(c3, isH ? T(0) : u[0]);                      // trip 0, L: M[0] = B*u[0] (m3 = b3*u0);  H: zeros
+        T r_new = xchg(pcur);                                         // H: m2 of step 0;  (L: unused)
         T wp = T(0), wq = T(0);
-        {
-            const T sp = A_::mul(qP, pcur), sq_ = A_::mul(qQ, qcur);
-            if (N - 1 > 0) IO::st2(pair_addr(0), sp, isH ? sq_ : T(0));
-        }
-        T recv = xchg(isH ? u[0] : pcur);                             // L gets u[1] (H's entry j = 0), H gets m2 of step 0
 #pragma unroll
-        for (int k = 1; k < N; ++k) {
-            // Y: L reads control entry k (own if k is even, received if odd); H reads L's m2 of step k-1
+        for (int k = 1; k <= N; ++k) {
+            // Y: L reads control entry k (own if k is even, received if odd); H reads L's m2 of step k-2
             T Y;
-            if (k & 1) Y = recv; else Y = isH ? recv : u[k / 2];
+            if (k == N) Y = isH ? r_old : T(0);                       // L has no step N: its numbers of this trip are unused
+            else if (k & 1) Y = r_old;
+            else Y = isH ? r_old : u[k / 2];
             const T pn = A_::madd(pcur, cP, qcur);
             const T t12 = A_::madd(A_::mul(c1, pcur), c2, qcur);
             T qn;
             if constexpr (EXACT) qn = A_::add(t12, A_::mul(c3, Y));
             else qn = isH ? A_::madd(qcur, c3, Y) : A_::add(t12, A_::mul(c3, Y));   // H: m1 + a12*m2 is one contracted term in FAST mode
             pcur = pn; qcur = qn;
-            const T sp = A_::mul(qP, pcur), sq_ = A_::mul(qQ, qcur);  // diagm(Q)*M[k], rows 0-1 (H)
-            if (k < N - 1) {
-                IO::st2(pair_addr(k), sp, sq_);
-                recv = xchg(isH ? u[k / 2] : pcur);                   // H's entry 2*(k/2)+1 == k+1 when k is even
-            } else { wp = sp; wq = sq_; }                             // the backward sweep starts from the scaled last step
+            // diagm(Q)*M[k-1], rows 0-1, on H; zeros on L (its pair slots must read as zero in the backward sweep)
+            const T sp = A_::mul(qP, pcur), sq_ = A_::mul(qQ, qcur);
+            IO::st2(pair_addr(k - 1), sp, sq_);
+            if (k == N) { wp = sp; wq = sq_; }                        // the backward sweep starts from the scaled last step
+            r_old = r_new;
+            if (k <= N - 2) {
+                // end of trip k: H sends the control entry of L's step k+2 (needed when k is odd), L sends m2 of step k
+                if (k & 1) r_new = xchg(isH ? u[(k + 1) / 2] : pcur);
+                else r_new = xchg(pcur);
+            }
         }
         // ---------------- backward sweep: M[i-1] += trans(A)*M[i] (mpc.h:281), gradient (mpc.h:283), stopping test
-        // (mpc.h:289-311) and provisional update (mpc.h:339-344) of the entry pairs (N-1-k, N-k) at odd k
-        pcur = wp; qcur = wq;                                         // step N-1: H (Q0*m0, Q1*m1), L (0, 0)
-        recv = xchg(qcur);                                            // L gets w1 of step N-1, H gets w3 of step N-1
+        // (mpc.h:289-311) and provisional update (mpc.h:339-344)
+        pcur = wp; qcur = wq;                                         // trip 0: H = step N-1 (Q0*m0, Q1*m1);  L = (0, 0)
+        r_old = T(0);                                                 // L's trip 1 keeps its zeros
+        r_new = xchg(qcur);                                           // end of trip 0: L gets w1 of step N-1, H gets w3 of step N-1 (0)
         bool notconv = false;
         unsigned long long nsat = 0;
+        // The shared-memory accesses are volatile (they must really go through shared memory, solve_kernel.cuh), so
+        // they issue in program order: a store waiting for the end of an update's dependency chain would hold back
+        // every later load.  Hence loads are issued one trip (stash) / one update (v) ahead of their use and an
+        // update's stores one update late, when their operands have long been ready.
+        T s0, s1;
+        IO::ld2(lag_addr(N - 2), s0, s1);                             // stash of trip 1
+        T vo = getV(NH - 1);                                          // v of the first update (trip 3)
+        T mmv = getMM(NH - 1);
+        T pend_u = T(0), pend_vold = T(0), pend_vn = T(0);            // the previous update's stores
 #pragma unroll
-        for (int k = 1; k < N; ++k) {
-            const int s = N - 1 - k;                                  // the step both lanes compute now
-            T s0, s1;
-            IO::ld2(pair_addr(s), s0, s1);
-            const T X = recv;                                         // L: w1 of step s+1;  H: w3 of step s+1
-            const T tt = A_::add(A_::mul(h1, X), pcur);
-            const T pn = A_::madd(tt, mc, isH ? s0 : qcur);
-            const T cq = A_::madd(A_::mul(g1, pcur), g2, qcur);
-            const T qn = A_::add(isH ? s1 : T(-0.0), cq);
-            pcur = pn; qcur = qn;
-            if (k & 1) {
-                // entries: H owns N-k (odd, its w3 arrived with the last exchange), L owns N-1-k == s (even, w3 just computed)
-                const int j = s / 2;
+        for (int k = 1; k <= N + 1; ++k) {
+            const T X = r_old;                                        // L: w1 of step N-k+1;  H: w3 of step N-k+2
+            T s0f = T(0), s1f = T(0);
+            if (k + 1 <= N) IO::ld2(lag_addr(N - 2 - k), s0f, s1f);   // stash of trip k+1
+            const bool upd = (k & 1) && k >= 3;
+            const int j = (N + 1 - k) / 2;                            // L: entry N+1-k = 2j, H: entry N+2-k = 2j+1
+            T vof = T(0), mmf = T(0);
+            if (upd && j >= 1) { vof = getV(j - 1); mmf = getMM(j - 1); }                             // for the update two trips on
+            if (upd && j + 1 <= NH - 1) { IO::st2(own_addr(j + 1), pend_u, pend_vold); setV(j + 1, pend_vn); }   // ... and of two trips ago
+            if (upd) {
                 const T w3 = isH ? X : qcur;
                 const T uij = u[j];
-                const T dfv = A_::add(A_::add(getMM(j), A_::mul(b3, w3)), A_::mul(R, uij));          // mpc.h:283
-                const T v_old = getV(j);
-                IO::st2(own_addr(j), uij, v_old);                      // the slot of this entry's step has been consumed
+                const T dfv = A_::add(A_::add(mmv, A_::mul(b3, w3)), A_::mul(R, uij));               // mpc.h:283
                 const bool big = absval(dfv) >= eps;
                 const bool blocked = ((sat >> j) & 1ull) != 0 && PS::sign_differs(dfv, uij);           // mpc.h:296-299
                 notconv |= big & !blocked;
                 const T t1 = A_::sub(uij, A_::mul(inv_lambda, dfv));                                   // mpc.h:341
                 const T vn = PS::clamp_sym(t1, hi, PS::inside(t1, hi));
-                const T t2 = A_::madd(vn, beta, A_::sub(vn, v_old));                                   // mpc.h:344
+                const T t2 = A_::madd(vn, beta, A_::sub(vn, vo));                                      // mpc.h:344
                 const bool in2 = PS::inside(t2, hi);
                 u[j] = PS::clamp_sym(t2, hi, in2);
                 nsat |= (unsigned long long)(!in2) << j;
-                setV(j, vn);
+                pend_u = uij; pend_vold = vo; pend_vn = vn;            // the slot of this entry's step has been consumed: stored next update
+                vo = vof; mmv = mmf;
             }
-            if (k < N - 1) recv = xchg(qcur);
+            if (k <= N) {
+                // H: step N-1-k from slot N-1-k;  L: step N-k, whose slot holds the zeros the forward sweep stored
+                // (a12*X + p) + s0 + mc*q  and  s1 + (g1*p + g2*q): on H the first term is 0*w3 + w0 and mc = 0,
+                // on L both stash words are zero
+                const T tt = A_::add(A_::mul(h1, X), pcur);
+                const T pn = A_::madd(A_::add(tt, s0), mc, qcur);
+                const T cq = A_::madd(A_::mul(g1, pcur), g2, qcur);
+                const T qn = A_::add(s1, cq);
+                pcur = pn; qcur = qn;
+            }
+            s0 = s0f; s1 = s1f;
+            r_old = r_new;
+            if (k <= N - 1) r_new = xchg(qcur);                       // end of trip k: H's w1 of step N-1-k, L's w3 of step N-k
         }
+        IO::st2(own_addr(0), pend_u, pend_vold); setV(0, pend_vn);    // the last update's stores
         sat = nsat;
         return __shfl_xor_sync(0xffffffffu, (int)notconv, 1) != 0 || notconv;
     }
@@ -230,6 +263,7 @@ pair_kernel(const __grid_constant__ SolveParams<T, 4, 1, N> p)
     sv.a1 = wb + (unsigned)lane * sizeof(T);
     sv.a2 = wb + (unsigned)lane * 2u * sizeof(T);
     sv.a2own = sv.a2 + (unsigned)(role * 2 * 32 * (int)sizeof(T));
+    sv.a2lag = sv.a2 + (unsigned)((1 - role) * 2 * 32 * (int)sizeof(T));
     sv.sat = 0;
     if constexpr (!PIM)
         sv.set_model(role != 0, p.A[1], p.A[6], p.A[11], p.A[14], p.A[15], p.B[3], p.Q[0], p.Q[1], p.R[0], p.hi[0], p.lambda, p.eps);

@@ -283,16 +283,39 @@ struct PgSolver {
         for (int j = 0; j < I; ++j) { lo_[j] = mLo(j); hi_[j] = mHi(j); }
         const Bits eps_bits = BitsOf<T>::to(p.eps);
         unsigned long long nsat = 0;
+        // The shared-memory accesses are volatile asm (they must really go through shared memory, solve_kernel.cuh), so
+        // they issue in program order, and a warp issues in order: a store waiting for the end of an entry's update
+        // chain (df -> v -> u, ~6 dependent operations) would hold back the stash load of the NEXT step's recursion, the
+        // pass's critical path.  So every load is issued one horizon step ahead of its use and a step's stores one step
+        // late, when their operands have long been ready (profiles/r2_experiments.md: lone-warp pass 3 050 -> ~2 300 cycles).
+        T vo[I], mmv[I], pu[I], pvo[I], pvn[I];
+#pragma unroll
+        for (int j = 0; j < I; ++j) { vo[j] = getV((N - 1) * I + j); mmv[j] = getMM((N - 1) * I + j); pu[j] = pvo[j] = pvn[j] = T(0); }
 #pragma unroll(L::UNR)
         for (int i = N - 1; i >= 0; --i) {
+            // ---- loads of this step's recursion and of the next step's update
+            T st[L::W];
+#pragma unroll
+            for (int q = 0; q < L::W; ++q) st[q] = T(0);
+            if (i > 0) {
+#pragma unroll
+                for (int q = 0; q < (L::SQ + 1) / 2; ++q) IO::ld2(pair_addr(L::O_QM + (i - 1) * L::W + 2 * q), st[2 * q], st[2 * q + 1]);
+            }
+            T vof[I], mmf[I];
+#pragma unroll
+            for (int j = 0; j < I; ++j) { vof[j] = T(0); mmf[j] = T(0); if (i > 0) { vof[j] = getV((i - 1) * I + j); mmf[j] = getMM((i - 1) * I + j); } }
+            // ---- stores of the previous step (i + 1): its stash slot was consumed a step ago
+            if (i < N - 1) {
+#pragma unroll
+                for (int j = 0; j < I; ++j) { IO::st2(pair_addr(L::O_QM + (i + 1) * L::W + 2 * j), pu[j], pvo[j]); setV((i + 1) * I + j, pvn[j]); }
+            }
 #pragma unroll
             for (int j = I - 1; j >= 0; --j) {
                 const int k = i * I + j;
                 T bt; const bool hbt = dotBT(j, w, bt);
                 const T uij = getU(k);
-                const T dfv = A_::add(add_opt(true, getMM(k), hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
-                const T v_old = getV(k);
-                IO::st2(pair_addr(L::O_QM + i * L::W + 2 * j), uij, v_old);      // this step's stash is consumed
+                const T dfv = A_::add(add_opt(true, mmv[j], hbt, bt), A_::mul(mR(j), uij));                     // mpc.h:283
+                const T v_old = vo[j];
                 T vn, un;
                 if constexpr (SYM) {
 #if BMPC_PG_IBIG
@@ -321,13 +344,12 @@ struct PgSolver {
                     vn = clamp_m(A_::sub(uij, A_::mul(inv_lambda, dfv)), lo_[j], hi_[j]);
                     un = clamp_m(A_::madd(vn, beta, A_::sub(vn, v_old)), lo_[j], hi_[j]);
                 }
-                setV(k, vn);
+                pu[j] = uij; pvo[j] = v_old; pvn[j] = vn;                 // stored during the next step
                 setU(k, un);
             }
-            if (i > 0) {
-                T st[L::W];
 #pragma unroll
-                for (int q = 0; q < (L::SQ + 1) / 2; ++q) IO::ld2(pair_addr(L::O_QM + (i - 1) * L::W + 2 * q), st[2 * q], st[2 * q + 1]);
+            for (int j = 0; j < I; ++j) { vo[j] = vof[j]; mmv[j] = mmf[j]; }
+            if (i > 0) {
                 T wn[S];
 #pragma unroll
                 for (int r = 0; r < S; ++r) {                                                                   // mpc.h:281
@@ -339,6 +361,8 @@ struct PgSolver {
                 for (int r = 0; r < S; ++r) w[r] = wn[r];
             }
         }
+#pragma unroll
+        for (int j = 0; j < I; ++j) { IO::st2(pair_addr(L::O_QM + 2 * j), pu[j], pvo[j]); setV(j, pvn[j]); }   // step 0's stores
         if constexpr (SYM) sat = nsat;
         return notconv;
     }
