@@ -6,9 +6,14 @@
 //   cpp/build/libtrajectory_point_controller.so   the re-hosted module (extraction on the GPU too)
 #include <dlfcn.h>
 
+#include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <memory>
+#include <vector>
 
 #include "lms/module.h"
 #include "phoenix_CC2016_service/phoenix_CC2016_service.h"
@@ -48,7 +53,10 @@ static void dump(int k, bool ok, const CarCommand& car, const TrajectoryPoint& p
 
 int main(int argc, char** argv)
 {
-    if (argc < 2) { std::fprintf(stderr, "usage: module_driver <module.so>\n"); return 64; }
+    if (argc < 2) { std::fprintf(stderr, "usage: module_driver <module.so> [--time CYCLES]\n"); return 64; }
+    // --time N: instead of dumping the 48-cycle scenario, time N tobiMPC cycles (the same scenario, repeated) and print
+    // the per-cycle latency of cycle() as one JSON line
+    const int timed = (argc >= 4 && std::strcmp(argv[2], "--time") == 0) ? std::atoi(argv[3]) : 0;
     void* so = dlopen(argv[1], RTLD_NOW | RTLD_GLOBAL);
     if (!so) { std::fprintf(stderr, "dlopen: %s\n", dlerror()); return 65; }
     typedef void* (*factory_t)();
@@ -70,7 +78,10 @@ int main(int argc, char** argv)
     mod->config().setArray<float>("mpcLookupVelocityY", {0.3f, 2.0f, 3.5f});
     if (!mod->initialize()) { std::fprintf(stderr, "initialize() failed\n"); return 2; }
 
-    for (int k = 0; k < 48; ++k) {
+    std::vector<double> lat;
+    const int cycles = timed > 0 ? timed + 50 : 48;
+    for (int kk = 0; kk < cycles; ++kk) {
+        const int k = timed > 0 ? (kk % 40 == 20 ? 21 : kk % 40) : kk;            // timing: tobiMPC cycles only (no IDLE / pid)
         const float v = 0.03f + 0.11f * k;
         car->setMeasured(v, 0.01f * k, -0.005f * k);
         *traj = path(24 + (k % 5) * 9, 0.05f + 0.01f * (k % 4), 0.05f + 0.02f * (k % 7), 0.7f + 0.1f * (k % 3),
@@ -80,8 +91,17 @@ int main(int argc, char** argv)
         mod->config().set<double>("weight_y", 20.0 + (k % 5));                      // live tuning (reference :92-95)
         mod->config().set<double>("weight_steering_rear", 10.0 - 0.5 * (k % 4));
         mod->config().set<std::string>("type", (k >= 40 && k < 44) ? "pid" : "tobiMPC");
+        const auto t0 = std::chrono::steady_clock::now();
         const bool ok = mod->cycle();
-        dump(k, ok, *car, *dbg);
+        const auto t1 = std::chrono::steady_clock::now();
+        if (timed > 0) { if (kk >= 50) lat.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count()); }
+        else dump(k, ok, *car, *dbg);
+    }
+    if (timed > 0) {
+        std::sort(lat.begin(), lat.end());
+        double sum = 0; for (double x : lat) sum += x;
+        std::printf("{\"module\": \"%s\", \"cycles\": %d, \"cycle_us\": {\"p50\": %.2f, \"p99\": %.2f, \"mean\": %.2f, \"min\": %.2f}}\n",
+                    argv[1], (int)lat.size(), lat[lat.size() / 2], lat[(size_t)(lat.size() * 0.99)], sum / lat.size(), lat.front());
     }
     mod->deinitialize();
     return 0;

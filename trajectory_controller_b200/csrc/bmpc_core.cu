@@ -342,10 +342,28 @@ int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C,
         if (bad) return fail(BMPC_E_INVALID, std::string("bmpc_set_model: ") + bad);
     }
     int rc;
-    if ((rc = upload_soa(h, A, cnt, S * S, h->mA)) || (rc = upload_soa(h, B, cnt, S * I, h->mB)) ||
-        (rc = upload_soa(h, C, cnt, S, h->mC)) || (rc = upload_soa(h, Q, cnt, S, h->mQ)) ||
-        (rc = upload_soa(h, R, cnt, I, h->mR)) || (rc = upload_soa(h, lower, cnt, I, h->mlo)) ||
-        (rc = upload_soa(h, upper, cnt, I, h->mhi)))
+    const int lens[7] = {S * S, S * I, S, S, I, I, I};
+    const double* srcs[7] = {A, B, C, Q, R, lower, upper};
+    DevBuf* bufs[7] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi};
+    int total = 0; for (int a = 0; a < 7; ++a) total += lens[a];
+    if (cnt == 1 && total <= kSmallVals) {
+        // one model (the facade's case, a fresh dlib::mpc per cycle() of the reference module): the numbers travel as
+        // kernel arguments — no staging copy, no synchronisation before the constructor kernel
+        SmallVals v; PutPlan plan; plan.n = 7;
+        int at = 0;
+        for (int a = 0; a < 7; ++a) {
+            BMPC_CUDA(bufs[a]->reserve((size_t)h->cap * lens[a] * h->elem));
+            plan.off[a] = at; plan.len[a] = lens[a]; plan.dst[a] = bufs[a]->p;
+            for (int e = 0; e < lens[a]; ++e) v.x[at + e] = srcs[a][e];
+            at += lens[a];
+        }
+        plan.off[7] = 0; plan.len[7] = 0; plan.dst[7] = nullptr;
+        BMPC_CUDA(put_vals(v, plan, 0, 1, h->cap, h->elem, h->stream));
+        h->launches++;
+    } else if ((rc = upload_soa(h, A, cnt, S * S, h->mA)) || (rc = upload_soa(h, B, cnt, S * I, h->mB)) ||
+               (rc = upload_soa(h, C, cnt, S, h->mC)) || (rc = upload_soa(h, Q, cnt, S, h->mQ)) ||
+               (rc = upload_soa(h, R, cnt, I, h->mR)) || (rc = upload_soa(h, lower, cnt, I, h->mlo)) ||
+               (rc = upload_soa(h, upper, cnt, I, h->mhi)))
         return rc;
     BMPC_CUDA(h->mlambda.reserve((size_t)h->cap * h->elem));
     BMPC_CUDA(h->mqdiag.reserve((size_t)h->cap * h->NI * h->elem));

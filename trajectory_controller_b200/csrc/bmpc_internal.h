@@ -54,6 +54,17 @@ cudaError_t launch_extract_horizon(long long count, int P, const int32_t* npoint
                                    long long stride_point, const float* d0, const float* step, int steps, int32_t* idx,
                                    uint8_t* flag, float* opx, float* opy, float* odx, float* ody, float* ovel, cudaStream_t st);
 
+// Small-call paths (layout_kernels.cu): values passed as kernel arguments.
+constexpr int kSmallVals = 64;
+struct SmallVals { double x[kSmallVals]; };
+struct PutPlan { int n; int off[8]; int len[8]; void* dst[8]; };
+cudaError_t put_vals(const SmallVals& v, const PutPlan& plan, long long first, long long count, long long stride, int elem_size,
+                     cudaStream_t st);
+constexpr int kSmallSolve = 16;    // solves of up to this many instances use the packed one-copy result path
+__host__ __device__ inline size_t small_results_err_offset(int count, int I) { return (((size_t)count * I * 8 + (size_t)count * 5) + 7) & ~(size_t)7; }
+cudaError_t pack_results(const void* u0, const uint32_t* iters, const uint8_t* status, const unsigned long long* queue, int count,
+                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st);
+
 const ShapeOps* find_shape(int S, int I, int N);
 const ShapeOps* select_pattern(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
                                long long count, bool as_float);

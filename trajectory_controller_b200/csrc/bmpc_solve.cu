@@ -30,10 +30,17 @@ int write_target_rows(bmpc_handle* h, void* dst_rows, const double* val, int per
         BMPC_CUDA(h->stage.reserve(bytes));
         BMPC_CUDA(cudaMemcpyAsync(h->stage.p, val, bytes, cudaMemcpyHostToDevice, h->stream));
         BMPC_CUDA(aos_to_soa((const double*)h->stage.p, dst_rows, count, S, h->cap, h->elem, h->stream));
+    } else if (S <= kSmallVals) {
+        // one vector for every instance: passed as a kernel argument (no staging copy to wait for)
+        SmallVals v; PutPlan plan{};
+        plan.n = 1; plan.off[0] = 0; plan.len[0] = S; plan.dst[0] = dst_rows;
+        for (int e = 0; e < S; ++e) v.x[e] = val[e];
+        BMPC_CUDA(put_vals(v, plan, 0, h->cap, h->cap, h->elem, h->stream));
     } else {
         std::memcpy(h->pinned, val, (size_t)S * 8);
         BMPC_CUDA(cudaMemcpyAsync(h->small.p, h->pinned, (size_t)S * 8, cudaMemcpyHostToDevice, h->stream));
         BMPC_CUDA(broadcast_rows((const double*)h->small.p, dst_rows, h->cap, S, h->cap, h->elem, h->stream));
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));           // the pinned mirror is free again
     }
     h->launches++;
     return BMPC_OK;
@@ -66,7 +73,9 @@ int bmpc_set_target(bmpc_t* h, const double* val, int time, int per_instance, in
         if ((rc = ensure_full_targets(h))) return rc;
         if ((rc = write_target_rows(h, (char*)h->target_full.p + row * slot_of(h, time), val, per_instance, count))) return rc;
     }
-    BMPC_CUDA(cudaStreamSynchronize(h->stream));               // `val` and the staging buffers are free again
+    // per-instance values went through the staging buffer, which the next call may reuse; a shared vector travelled
+    // as a kernel argument and needs no wait (the call is stream-ordered like every other)
+    if (per_instance) BMPC_CUDA(cudaStreamSynchronize(h->stream));
     return BMPC_OK;
 }
 
@@ -94,8 +103,7 @@ int bmpc_reset(bmpc_t* h)
     BMPC_CUDA(cudaMemsetAsync(h->target_const.p, 0, h->target_const.bytes, h->stream));
     if (h->full_targets) BMPC_CUDA(cudaMemsetAsync(h->target_full.p, 0, h->target_full.bytes, h->stream));
     h->head = 0;
-    BMPC_CUDA(cudaStreamSynchronize(h->stream));
-    return BMPC_OK;
+    return BMPC_OK;                     // stream-ordered: nothing of the caller's is referenced, nothing to wait for
 }
 
 int bmpc_get_controls(bmpc_t* h, int64_t first, int64_t count, double* controls)
@@ -302,9 +310,41 @@ int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t
     return BMPC_OK;
 }
 
+// A solve of a few instances (the facade's operator(), count = 1): x0 travels as a kernel argument and the results come
+// back in ONE packed copy — two launches and one synchronisation around the solve kernels.
+static int small_solve(bmpc_t* h, int count, const double* x0, double* u0, uint32_t* iters, uint8_t* status, unsigned flags)
+{
+    BMPC_CUDA(cudaSetDevice(h->device));
+    SmallVals v; PutPlan plan{};
+    for (int b = 0; b < count; ++b) {        // one launch per instance keeps the argument block small; count is tiny
+        plan.n = 1; plan.off[0] = 0; plan.len[0] = h->S; plan.dst[0] = h->x0.p;
+        for (int e = 0; e < h->S; ++e) v.x[e] = x0[(size_t)b * h->S + e];
+        BMPC_CUDA(put_vals(v, plan, b, 1, h->cap, h->elem, h->stream));
+        h->launches++;
+    }
+    int rc = bmpc_solve_resident_async(h, count, flags);
+    if (rc) return rc;
+    const size_t err_off = small_results_err_offset(count, h->I), bytes = err_off + 8;
+    BMPC_CUDA(pack_results(h->u0.p, (const uint32_t*)h->iters.p, (const uint8_t*)h->status.p, (const unsigned long long*)h->queue.p,
+                           count, h->I, h->cap, h->elem, (unsigned char*)h->small.p, h->stream));
+    h->launches++;
+    unsigned char* pin = (unsigned char*)h->pinned;
+    BMPC_CUDA(cudaMemcpyAsync(pin, h->small.p, bytes, cudaMemcpyDeviceToHost, h->stream));
+    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    std::memcpy(u0, pin, (size_t)count * h->I * 8);
+    if (iters) std::memcpy(iters, pin + (size_t)count * h->I * 8, (size_t)count * 4);
+    if (status) std::memcpy(status, pin + (size_t)count * h->I * 8 + (size_t)count * 4, (size_t)count);
+    unsigned long long err; std::memcpy(&err, pin + err_off, 8);
+    if (err) { h->ring_dirty = true; return fail(BMPC_E_STATE, "bmpc_solve: the solve gave up (hand-over ring overrun); results are incomplete"); }
+    return BMPC_OK;
+}
+
 int bmpc_solve(bmpc_t* h, int64_t count, const double* x0, double* u0, uint32_t* iters, uint8_t* status, unsigned flags)
 {
     int rc;
+    if (h && x0 && u0 && count >= 1 && count <= kSmallSolve && count <= h->cap && (long long)h->S <= kSmallVals &&
+        small_results_err_offset((int)count, h->I) + 8 <= h->pinned_bytes)
+        return small_solve(h, (int)count, x0, u0, iters, status, flags);
     if ((rc = upload_x0_async(h, count, x0))) return rc;   // x0 stays valid: bmpc_download synchronises before returning
     if ((rc = bmpc_solve_resident_async(h, count, flags))) return rc;
     return bmpc_download(h, count, u0, iters, status);
@@ -393,6 +433,35 @@ int bmpc_extract_points(bmpc_t* h, int64_t count, int P, const int32_t* npoints,
     if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, "bmpc_extract_points: null trajectory array");
     if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, "bmpc_extract_points: negative stride");
     BMPC_CUDA(cudaSetDevice(h->device));
+    if (count == 1 && stride_point == 1 && (size_t)P * 20 + 64 <= h->pinned_bytes / 2) {
+        // One polyline (the module's getTrajectoryPoint): the five arrays and the distance are packed into the pinned
+        // mirror and cross in ONE copy each way instead of six in and seven out.
+        int n = npoints ? npoints[0] : P;
+        if (n > P) n = P;
+        if (n < 0) n = 0;
+        float* pin = (float*)h->pinned;
+        const float* src1[5] = {px, py, dx, dy, vel};
+        for (int a = 0; a < 5; ++a)
+            if (n) std::memcpy(pin + (size_t)a * n, src1[a], (size_t)n * 4);
+        pin[(size_t)5 * n] = dist[0];
+        const size_t in_bytes = ((size_t)5 * n + 1) * 4;
+        BMPC_CUDA(h->ex[0].reserve(in_bytes));
+        BMPC_CUDA(h->ex[7].reserve(32));
+        BMPC_CUDA(cudaMemcpyAsync(h->ex[0].p, pin, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        const float* d = (const float*)h->ex[0].p;
+        unsigned char* o = (unsigned char*)h->ex[7].p;
+        BMPC_CUDA(launch_extract(1, n, nullptr, d, d + n, d + 2 * (size_t)n, d + 3 * (size_t)n, d + 4 * (size_t)n, 0, 1, d + 5 * (size_t)n,
+                                 (int32_t*)o, (uint8_t*)(o + 4), (float*)(o + 8), (float*)(o + 12), (float*)(o + 16), (float*)(o + 20),
+                                 (float*)(o + 24), h->stream));
+        h->launches++;
+        unsigned char* back = (unsigned char*)h->pinned + h->pinned_bytes / 2;
+        BMPC_CUDA(cudaMemcpyAsync(back, o, 32, cudaMemcpyDeviceToHost, h->stream));
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));
+        std::memcpy(idx, back, 4); *flag = back[4];
+        std::memcpy(out_px, back + 8, 4); std::memcpy(out_py, back + 12, 4); std::memcpy(out_dx, back + 16, 4);
+        std::memcpy(out_dy, back + 20, 4); std::memcpy(out_vel, back + 24, 4);
+        return BMPC_OK;
+    }
     const size_t nflt = P > 0 ? (size_t)((count - 1) * stride_instance + (int64_t)(P - 1) * stride_point + 1) : 0;
     const float* src[5] = {px, py, dx, dy, vel};
     for (int a = 0; a < 5; ++a) {

@@ -202,6 +202,37 @@ __global__ void k_extract_horizon(long long count, int P, const int32_t* __restr
     }
 }
 
+// ---- small-call paths: a handful of numbers travel as KERNEL ARGUMENTS instead of through a staging copy, so that a
+// capacity-1 controller (the dlib::mpc facade, one object per cycle() in the reference module) pays no H2D copy and no
+// stream synchronisation for its inputs.
+// vals[off[a] .. off[a] + len[a]) -> dst[a][e * stride + b] for b in [first, first + count): `count` == capacity
+// broadcasts one vector to every instance (set_target(val)), count == 1 writes one instance (shared model, x0).
+template <typename T>
+__global__ void k_put_vals(SmallVals v, PutPlan plan, long long first, long long count, long long stride)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= count) return;
+    for (int a = 0; a < plan.n; ++a) {
+        T* dst = reinterpret_cast<T*>(plan.dst[a]);
+        for (int e = 0; e < plan.len[a]; ++e) dst[(long long)e * stride + first + b] = (T)v.x[plan.off[a] + e];
+    }
+}
+// Results of a small solve, packed for ONE device-to-host copy: [count][I] doubles | iters u32[count] | status u8[count]
+// (padded to 8) | the launch's error word (queue[4]).
+template <typename T>
+__global__ void k_pack_results(const T* __restrict__ u0, const uint32_t* __restrict__ iters, const uint8_t* __restrict__ status,
+                               const unsigned long long* __restrict__ queue, int count, int I, long long stride, unsigned char* out)
+{
+    const int t = threadIdx.x;
+    double* ou = reinterpret_cast<double*>(out);
+    uint32_t* oi = reinterpret_cast<uint32_t*>(out + (size_t)count * I * 8);
+    uint8_t* os = out + (size_t)count * I * 8 + (size_t)count * 4;
+    unsigned long long* oe = reinterpret_cast<unsigned long long*>(out + small_results_err_offset(count, I));
+    for (int f = t; f < count * I; f += blockDim.x) ou[f] = (double)u0[(long long)(f % I) * stride + f / I];
+    for (int b = t; b < count; b += blockDim.x) { oi[b] = iters[b]; os[b] = status[b]; }
+    if (t == 0) *oe = queue[4];
+}
+
 inline unsigned blocks_for(long long count, int block) { return (unsigned)((count + block - 1) / block); }
 }  // namespace
 
@@ -257,6 +288,23 @@ cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const
     if (count <= 0) return cudaSuccess;
     k_extract<<<blocks_for(count, 128), 128, 0, st>>>(count, P, npoints, px, py, dx, dy, vel, stride_instance,
                                                      stride_point, dist, idx, flag, opx, opy, odx, ody, ovel);
+    return cudaGetLastError();
+}
+
+cudaError_t put_vals(const SmallVals& v, const PutPlan& plan, long long first, long long count, long long stride, int elem_size,
+                     cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    const int block = count < 128 ? 32 : 128;
+    if (elem_size == 8) k_put_vals<double><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride);
+    else k_put_vals<float><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride);
+    return cudaGetLastError();
+}
+cudaError_t pack_results(const void* u0, const uint32_t* iters, const uint8_t* status, const unsigned long long* queue, int count,
+                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st)
+{
+    if (elem_size == 8) k_pack_results<double><<<1, 64, 0, st>>>((const double*)u0, iters, status, queue, count, I, stride, out);
+    else k_pack_results<float><<<1, 64, 0, st>>>((const float*)u0, iters, status, queue, count, I, stride, out);
     return cudaGetLastError();
 }
 
