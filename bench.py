@@ -437,6 +437,17 @@ def run_ours(args):
                          "exact_mode_ceiling_frac": 0.5 if args.mode == "exact" else 1.0,
                          "kernel": kname, "kernel_ms": kernel_ms, "kernel_share_of_step": share_b if stage_b_ms > 0 else 1.0,
                          "algorithmic_flops_per_launch": kflops,
+                         # what the hardware executes for one algorithmic unit (one iteration of one instance): the
+                         # pattern-specialised EXACT kernel drops the structural zeros / ones of the bicycle model, so it
+                         # executes fewer flops than the dense count `achieved` is defined on, and it
+                         # may not fuse (1 flop per instruction) — profiles/r2_sass_mix_pg_kernel.txt, pass loop only
+                         "executed": {"fp64_pipe_instructions_per_unit": 1033 if (args.precision == 64 and args.mode == "exact") else None,
+                                      "flops_per_unit": 943 if (args.precision == 64 and args.mode == "exact") else None,
+                                      "algorithmic_flops_per_unit": int(W.flops_per_iteration(S_, I_, N_)),
+                                      "fp64_pipe_instr_per_s": (1033.0 * float(np.maximum(iters - 50, 0).sum()) / (kernel_ms * 1e-3) / 1e9)
+                                      if (args.precision == 64 and args.mode == "exact" and stage_b_ms > 0) else None,
+                                      "unit": "G thread-instructions/s (compare peak_ginstr_unfused)",
+                                      "source": "SASS of pg_kernel<double,4,1,30,EXACT,bicycle4,SYM>: 488 DMUL + 455 DADD + 90 DSETP per pass"},
                          "hbm_bytes_per_launch_algorithmic": B * (S_ * 8 * 2 + I_ * 8 + 5) + (B * 3 * N_ * I_ * 8 * 2 if stage_b_ms > 0 else 0),
                          "launch": klaunch,
                          "whole_solve": {"achieved": achieved_solve, "frac": achieved_solve / peak_tf,

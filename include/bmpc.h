@@ -82,16 +82,22 @@ int bmpc_set_model(bmpc_t* h, const double* A, const double* B, const double* C,
  * dropping those terms is exact in IEEE arithmetic (only the sign of a zero can differ), so parity is unaffected.
  * enable = 0 forces the dense kernel (takes effect at the next bmpc_set_model).  Default: enabled. */
 int bmpc_set_specialization(bmpc_t* h, int enable);
-/* Two-stage solve (engine extension; default enabled).  When the shape offers it (horizon short enough for the
- * controls and the linear term to live in registers), a solve runs as two kernels: stage A = set-up (mpc.h:258-266)
- * plus the 50 coordinate steps (mpc.h:319-335), stage B = the projected-gradient phase (mpc.h:336-345) in a kernel
- * specialised for it.  For batches of one to four instances per resident lane, stage B also time-slices: every
- * 128 iterations a warp parks its instances at the tail of a work ring and resumes the oldest parked ones, so that
- * heavy-tailed iteration counts do not leave most lanes idle behind a few late long solves.  Results are
- * bit-identical to the one-kernel solve in every setting.  enable: 0 = one kernel; 1 = two-stage with fairness slices,
- * retirement of surplus warps near the end of a launch and, for models with lower == -upper, the symmetric-bound
- * stage-B kernel (default); 2 = two-stage, every instance runs to completion in the lane that claimed it; 3 = like 1
- * with the literal stage-B kernel whatever the bounds (2 and 3 exist for A/B tests). */
+/* Staged solve (engine extension; default enabled).  A solve runs as up to three kernels:
+ *   stage A  set-up (mpc.h:258-266) plus the 50 coordinate steps (mpc.h:319-335), one instance per lane;
+ *   stage B  the projected-gradient phase (mpc.h:336-345), one instance per lane, in a kernel specialised for it.  For
+ *            batches of one to four instances per resident lane it time-slices: every 128 iterations a warp parks its
+ *            instances at the tail of a work ring and resumes the oldest parked ones, so that heavy-tailed iteration
+ *            counts do not leave most lanes idle behind a few late long solves;
+ *   stage C  the same phase with one instance per LANE PAIR (block-triangular (4,1) models with symmetric bounds, even
+ *            horizons: the synthetic bicycle model of every (4,1,N) configuration): ~40 % less latency per iteration at
+ *            ~30 % more issue slots per instance.  It takes the last sm_count*64 unfinished instances of every launch
+ *            from stage B, and replaces stage B for batches up to that size, for per-instance models and for horizons
+ *            whose controls do not fit a lane's registers (N >= 60 in FP64).
+ * Results are bit-identical to the one-kernel solve in every setting.  enable: 0 = one kernel; 1 = staged with fairness
+ * slices, retirement of surplus warps near the end of a launch, the symmetric-bound stage-B kernel for models with
+ * lower == -upper, and stage C (default); 2 = stages A + B only, every instance runs to completion in the lane that
+ * claimed it; 3 = like 2 with fairness slices and retirement, but the literal stage-B kernel whatever the bounds
+ * (2 and 3 exist for A/B tests). */
 int bmpc_set_split(bmpc_t* h, int enable);
 /* Name of the pattern the current model runs with: "dense", "bicycle4", "tobi", "kat". */
 const char* bmpc_pattern_name(bmpc_t* h);

@@ -278,16 +278,18 @@ def test_persistent_controllers_vs_oracle(oracle, which):
 
 # ------------------------------------------------------------------------------------------ full size, properties
 def test_config2_full_batch_properties(oracle):
-    """BASELINE config 2 at full size (65,536 cold instances, N=30, FP64): spot-check 768 instances against the
-    oracle, then size-independent properties: box feasibility, determinism, batch-order independence."""
+    """BASELINE config 2 at full size (65,536 cold instances, N=30, FP64): EVERY instance against the oracle (u0 value-
+    exact, identical iteration counts; a few seconds on the host cores), then size-independent properties: box
+    feasibility, determinism, batch-order independence.  The launch runs all three stages (stage B hands its last
+    instances to the lane-pair kernel)."""
+    import os
     bike, N, B = W.bicycle4_model(), 30, 65536
     x0 = W.random_offsets_x0(B, 42)
     with BatchedMPC(4, 1, N, B) as eng:
         eng.set_model(bike)
         u0, it, st = eng.solve(x0)
-        pick = np.random.default_rng(0).choice(B, 768, replace=False)
-        uo, _, ito, _ = oracle.batch_cold(bike, N, x0[pick], nthreads=8, want_controls=False)
-        assert same_values(u0[pick], uo) and np.array_equal(it[pick], ito)
+        uo, _, ito, _ = oracle.batch_cold(bike, N, x0, nthreads=os.cpu_count() or 8, want_controls=False)
+        assert same_values(u0, uo) and np.array_equal(it, ito)
         assert np.all(np.abs(u0) <= W.ALPHA_MAX) and np.all(it <= 10000) and np.all(st == 0)
         u1, it1, _ = eng.solve(x0)                                      # determinism / no state leaks in cold mode
         assert np.array_equal(u0.view(np.uint64), u1.view(np.uint64)) and np.array_equal(it, it1)
@@ -450,10 +452,14 @@ def test_split_solve_equals_one_kernel(shape):
 # ------------------------------------------------------------------------------------------ tolerance modes
 def test_tolerance_modes_fast_and_fp32(oracle):
     """BASELINE configs[2] in small: FP64 FAST (FMA allowed) and the two FP32 modes against the FP64 EXACT result (itself
-    checked against the oracle here).  Stated tolerances (north star): |du0| <= 1e-6 rad in FP64 mode, <= 1e-3 rad in FP32
-    mode.  FP64 FAST meets its bar with seven orders of margin and identical iteration counts.  FP32 meets 1e-3 at the
-    99.9th percentile; its maximum is set by solves whose stopping test (max_df < eps, mpc.h:310) trips dozens of
-    iterations earlier or later than in FP64 while u0 is still moving — bounded here at 2e-2 and reported in DESIGN.md §8."""
+    checked against the oracle here).  Stated tolerances (north star): |du0| <= 1e-6 rad in FP64 mode, <= 1e-3 rad in FP32.
+      FP64 FAST : bar MET with seven orders of margin and identical iteration counts — this is the engine's fast mode.
+      FP32      : bar NOT MET at the maximum (6.4e-3 over 1,048,576 instances, profiles/r2_cfg3_n*.json); met at the
+                  99.9th percentile (5e-4).  The outliers are solves whose stopping test (max_df < eps, mpc.h:310) trips
+                  dozens of iterations earlier or later than in FP64 while u0 is still moving: dlib's result is the
+                  iterate at ITS trip point, not the optimum, so no FP32 trajectory can reproduce it to 1e-3 without
+                  finishing in FP64.  The asserts below pin what FP32 does deliver (p99.9 <= 1e-3, max <= 2e-2, mean
+                  <= 1e-4); README / DESIGN.md / bench.py report FP32 as failing the north-star bar."""
     from trajectory_controller_b200.engine import FAST, FP32
     bike, N, B = W.bicycle4_model(), 30, 20000
     x0 = W.random_offsets_x0(B, 43)
@@ -481,14 +487,15 @@ def test_tolerance_modes_fast_and_fp32(oracle):
 
 def test_config3_one_million_instances_properties(oracle):
     """BASELINE configs[2] at this rank's full size (1,048,576 cold instances, seed 43, FP64 EXACT; stage B runs without
-    time slicing at this size): spot check against the oracle, box feasibility, and the mirror symmetry x0 -> -x0."""
+    time slicing at this size): 65,536 of them against the oracle, box feasibility, and the mirror symmetry x0 -> -x0."""
     bike, N, B = W.bicycle4_model(), 30, 1 << 20
     x0 = W.random_offsets_x0(B, 43)
     with BatchedMPC(4, 1, N, B) as eng:
         eng.set_model(bike)
         u0, it, st = eng.solve(x0)
-        pick = np.random.default_rng(3).choice(B, 384, replace=False)
-        uo, _, ito, _ = oracle.batch_cold(bike, N, x0[pick], nthreads=8, want_controls=False)
+        import os
+        pick = np.random.default_rng(3).choice(B, 65536, replace=False)
+        uo, _, ito, _ = oracle.batch_cold(bike, N, x0[pick], nthreads=os.cpu_count() or 8, want_controls=False)
         assert same_values(u0[pick], uo) and np.array_equal(it[pick], ito)
         assert np.all(np.abs(u0) <= W.ALPHA_MAX) and np.all(st == 0) and it.max() <= 10000
         u1, it1, _ = eng.solve(-x0)
