@@ -396,7 +396,8 @@ def run_ours(args):
         share_b = stage_b_ms / (stage_a_ms + stage_b_ms)
         kernel_ms = ms_launch * share_b
         kflops = float(W.flops_per_iteration(S_, I_, N_) * np.maximum(iters - 50, 0).sum())
-        kname = f"pg_kernel<{tname},{S_},{I_},{N_},{mname},shared-model>"
+        kname = (f"pg_kernel<{tname},{S_},{I_},{N_},{mname},shared-model> (stage B, one instance per lane) + "
+                 f"pair_kernel<{tname},{N_},{mname}> (stage C, its last instances on lane pairs): the projected-gradient phase")
         klaunch = info_b
     else:
         share_b, kernel_ms, kflops, klaunch = 0.0, ms_launch, flops, info
@@ -414,6 +415,9 @@ def run_ours(args):
     traffic, traffic_src = (None, None)
     if args.precision == 64 and args.mode == "exact" and B == BATCH:
         traffic, traffic_src = ncu_traffic("pg_kernel" if stage_b_ms > 0 else "solve_kernel", build_id)
+        if stage_b_ms > 0 and traffic is not None:                      # stage C belongs to the same phase
+            t2, _ = ncu_traffic("pair_kernel", build_id)
+            traffic += t2 or 0.0
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": 1e3 * t_res / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic", "config": config_dict(args, world),
