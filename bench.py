@@ -76,9 +76,10 @@ class ClockSampler(threading.Thread):
     """nvidia-smi SM clock + throttle reasons, sampled while the timed region runs."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active"
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, period: float = 0.05):
         super().__init__(daemon=True)
         self.index, self.stop_flag, self.samples, self.reasons, self.maxmhz = index, threading.Event(), [], set(), None
+        self.period = period
 
     def run(self):
         names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
@@ -96,7 +97,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            self.stop_flag.wait(0.05)
+            self.stop_flag.wait(self.period)
 
     def result(self):
         self.stop_flag.set(); self.join(timeout=6)
@@ -280,7 +281,11 @@ def run_ours(args):
             eng.solve_resident_async(B)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
         barrier()
-        sampler = ClockSampler(local); sampler.start()
+        # one sampler per job: every sample forks nvidia-smi, and 8 ranks x 20 forks/s would starve the host threads
+        # that drive the end-to-end loop
+        sampler = ClockSampler(local, period=0.05 if world == 1 else 0.25)
+        if rank == 0:
+            sampler.start()
         l0 = eng.launch_count()
         for a, b in ev:
             flush.zero_()
@@ -312,19 +317,27 @@ def run_ours(args):
         # arrays into pinned host memory on every rank — every rank ends the step holding the whole job's results.
         gather = None
         if world > 1:
-            du0, dit, dst = (torch.as_tensor(v, device=dev) for v in eng.device_results())
-            g_u0 = torch.empty((world * I_, B), dtype=du0.dtype, device=dev)
-            g_it = torch.empty((world * B,), dtype=torch.int32, device=dev)
-            g_st = torch.empty((world * B,), dtype=torch.uint8, device=dev)
-            h_u0 = torch.empty((world * I_, B), dtype=du0.dtype).pin_memory()
-            h_it = torch.empty((world * B,), dtype=torch.int32).pin_memory()
-            h_st = torch.empty((world * B,), dtype=torch.uint8).pin_memory()
+            # u0 | iters | status of a rank are one device allocation (bmpc_device_results_block): ONE all_gather, one D2H
+            blk_view, off_it, off_st = eng.device_results_block()
+            dblk = torch.as_tensor(blk_view, device=dev)
+            nblk = dblk.numel()
+            g_blk = torch.empty((world, nblk), dtype=torch.uint8, device=dev)
+            h_blk = torch.empty((world, nblk), dtype=torch.uint8).pin_memory()
+
+            gstream = torch.cuda.Stream(device=dev)
+            ev_solved, ev_gathered = torch.cuda.Event(), torch.cuda.Event()
 
             def gather():
-                dist.all_gather_into_tensor(g_u0, du0)
-                dist.all_gather_into_tensor(g_it, dit)
-                dist.all_gather_into_tensor(g_st, dst)
-                h_u0.copy_(g_u0, non_blocking=True); h_it.copy_(g_it, non_blocking=True); h_st.copy_(g_st, non_blocking=True)
+                # The collective runs on a side stream after the solve; the next step may start once the all_gather has
+                # read this rank's block (ev_gathered), while the D2H of the gathered blocks overlaps that next solve.
+                # Everything is complete before the timed region ends (both streams are synchronised there).
+                ev_solved.record(stream); gstream.wait_event(ev_solved)
+                with torch.cuda.stream(gstream):
+                    dist.all_gather_into_tensor(g_blk.view(-1), dblk)
+                    ev_gathered.record(gstream)
+                    if rank == 0:                      # every rank holds the job's results in HBM; rank 0 also on the host
+                        h_blk.copy_(g_blk, non_blocking=True)
+                stream.wait_event(ev_gathered)
         for _ in range(min(Wm, 3)):
             eng.solve(px0.numpy(), out=out)
             if gather:
@@ -336,23 +349,34 @@ def run_ours(args):
             if gather:
                 gather()
         stream.synchronize()
+        if gather:
+            gstream.synchronize()
         t_e2e_local = time.perf_counter() - t0
         barrier()
         t_e2e = max_over_ranks(t_e2e_local)
-        clocks = sampler.result()
+        clocks = sampler.result() if rank == 0 else None
         gather_info = None
         if gather:
             # the gathered copy must be what each rank computed: rank r's block equals its own results
-            ok = bool(np.array_equal(h_u0.numpy()[rank * I_:(rank + 1) * I_].T, out[0]) and
-                      np.array_equal(h_it.numpy()[rank * B:(rank + 1) * B].view(np.uint32), out[1]))
-            gev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
+            gstream.synchronize()
+            mine_blk = g_blk[rank].cpu().numpy() if rank != 0 else h_blk.numpy()[rank]
+            es = 8 if args.precision == 64 else 4
+            g_u = mine_blk[: B * I_ * es].view(np.float64 if es == 8 else np.float32).reshape(I_, B).T.astype(np.float64)
+            g_i = mine_blk[off_it: off_it + 4 * B].view(np.uint32)
+            ok = bool(np.array_equal(g_u, out[0]) and np.array_equal(g_i, out[1]))
+            # the collective alone, ranks aligned by a barrier (otherwise the first one measures the skew between ranks)
+            gev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(6)]
             for a, b in gev:
-                a.record(stream); gather(); b.record(stream)
+                barrier()
+                a.record(stream); gather(); stream.wait_stream(gstream); b.record(stream)
             stream.synchronize()
-            gms = max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in gev])))
-            gather_info = {"ms": gms, "bytes_per_rank_out": world * B * (I_ * du0.element_size() + 5),
+            gms = max_over_ranks(float(np.median([a.elapsed_time(b) for a, b in gev[1:]])))
+            gather_info = {"ms": gms, "bytes_per_rank_out": int(world * nblk),
                            "own_block_matches": bool(max_over_ranks(0.0 if ok else 1.0) == 0.0),
-                           "what": "3 x ncclAllGather (u0, iters, status) from HBM + D2H of the gathered arrays, inside e2e"}
+                           "what": "one ncclAllGather of every rank's result block (u0 | iters | status, one allocation) from HBM "
+                                   "(afterwards every rank holds the whole job's results in HBM) + one D2H of the gathered blocks into pinned host "
+                                   "memory on rank 0 (side stream: the copy overlaps the next step's solve), inside e2e; every rank's own "
+                                   "results also reach its host buffers through bmpc_solve"}
 
         # ---------------- single-solve latency through the ABI (batch of 1, cold) ----------------------------------
         lat = []
@@ -423,7 +447,7 @@ def run_ours(args):
             "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic", "config": config_dict(args, world),
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / K, "h2d_bytes_per_step": world * B * S_ * 8,
-                    "d2h_bytes_per_step": world * B * (I_ * 8 + 4 + 1) * (1 + (world if world > 1 else 0)),
+                    "d2h_bytes_per_step": world * B * (I_ * 8 + 4 + 1) + (world * int(nblk) if world > 1 else 0),
                     "api": "bmpc_solve (C ABI, pinned host buffers)" + (" + final result gather (NCCL all_gather + D2H on every rank)" if world > 1 else ""),
                     "gather": gather_info},
             "gpu_launches": int(launches),

@@ -140,6 +140,10 @@ int bmpc_sync(bmpc_t* h);
  * status as uint8[capacity].  Valid until bmpc_destroy; written by every solve on the handle's stream.  Any pointer
  * argument may be NULL. */
 int bmpc_device_results(bmpc_t* h, void** u0, void** iters, void** status);
+/* The three arrays above live in ONE device allocation, u0 first: `base` = its address (== u0), `bytes` its size,
+ * iters at base + iters_offset, status at base + status_offset (offsets are multiples of 256).  A multi-GPU host
+ * gathers a whole job's results with one collective and one device-to-host copy of this block per rank. */
+int bmpc_device_results_block(bmpc_t* h, void** base, uint64_t* bytes, uint64_t* iters_offset, uint64_t* status_offset);
 /* Run every later call of this handle on the caller's CUDA stream (a cudaStream_t passed as void*; NULL = back to
  * the handle's own stream).  Lets a host application order the engine with its own copies/events, and lets a
  * benchmark bracket launches with its own events.  The handle never destroys a borrowed stream. */

@@ -67,6 +67,14 @@ class Job:
         t.numpy()[...] = a
         return t
 
+    def sampler(self):
+        """Clock / throttle sampler of the job: rank 0 only (every sample forks nvidia-smi; eight samplers starve the host)."""
+        if self.rank != 0:
+            return None
+        sm = ClockSampler(self.local, period=0.05 if self.world == 1 else 0.25)
+        sm.start()
+        return sm
+
     def close(self):
         if self.world > 1:
             self.dist.destroy_process_group()
@@ -131,7 +139,7 @@ def tolerance(job: Job, args):
     cap = (B + world - 1) // world
     bike = W.bicycle4_model()
     res, ref = {}, None
-    sampler = ClockSampler(job.local); sampler.start()
+    sampler = job.sampler()
     for name, prec, mode in (("fp64_exact", FP64, EXACT), ("fp64_fast", FP64, FAST), ("fp32_exact", FP32, EXACT), ("fp32_fast", FP32, FAST)):
         with BatchedMPC(4, 1, 30, cap, prec, mode, device=job.local) as eng:
             eng.set_model(bike)
@@ -149,13 +157,13 @@ def tolerance(job: Job, args):
                      "gather_bytes_per_rank": g.bytes_out}
     return {"config": f"configs[2]: tolerance study, {B} cold (4,1,30) instances (seed 43) sharded round-robin over {world} GPU(s); "
                       "deltas vs FP64 EXACT (== dlib bit for bit) on the whole gathered batch", "bars": {"fp64": 1e-6, "fp32": 1e-3},
-            "results": res, "clocks": sampler.result()}
+            "results": res, "clocks": sampler.result() if sampler else None}
 
 
 def sweep(job: Job, args):
     world, rank = job.world, job.rank
     out = {}
-    sampler = ClockSampler(job.local); sampler.start()
+    sampler = job.sampler()
     for N in (10, 30, 60, 100):
         models, x0 = W.sweep_models(N, args.per_combo, 44)
         B = len(x0)
@@ -178,7 +186,7 @@ def sweep(job: Job, args):
                         "set_model_s_incl_ctor_kernel_and_h2d": t_model, "u0_checksum": float(np.abs(u0).sum())}
     return {"config": f"configs[3]: horizon x (w_y, w_psi, R) grid, 64 combos x {args.per_combo} x0 (seed 44), per-instance models "
                       f"(constructor math on the device), FP64 EXACT, sharded round-robin over {world} GPU(s)", "results": out,
-            "clocks": sampler.result()}
+            "clocks": sampler.result() if sampler else None}
 
 
 def closed(job: Job, args):
@@ -188,7 +196,7 @@ def closed(job: Job, args):
     pose0 = W.closed_loop_poses(count, 45, path)
     a, b = sharding.shard_range(count, rank, world)
     n = b - a
-    sampler = ClockSampler(job.local); sampler.start()
+    sampler = job.sampler()
     with BatchedMPC(4, 1, 30, n, FP64, EXACT, device=job.local) as eng:
         eng.set_model(W.bicycle4_model())
         eng.cl_init(path, pose0[a:b])
@@ -213,7 +221,7 @@ def closed(job: Job, args):
             "solves_per_s": nsolves / dt, "ms_per_tick": dt / (ticks - 5) * 1e3, "ms_per_tick_without_gather": t_run / (ticks - 5) * 1e3,
             "gather_ms": (dt - t_run) * 1e3, "kernel_launches_per_rank": int(launches),
             "iters_mean_per_solve": float(itot.sum() / (count * ticks)), "iters_max": int(imax.max()),
-            "max_distance_to_path_m": float(d.max()), "pose_checksum": float(np.abs(pose).sum()), "clocks": sampler.result()}
+            "max_distance_to_path_m": float(d.max()), "pose_checksum": float(np.abs(pose).sum()), "clocks": sampler.result() if sampler else None}
 
 
 def main():

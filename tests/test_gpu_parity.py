@@ -313,6 +313,24 @@ def test_ragged_batches_and_capacity(oracle):
             assert same_values(u0, uo[:cnt]) and np.array_equal(it, ito[:cnt]), cnt
 
 
+def test_device_results_block_layout():
+    """u0 | iters | status of a handle are one device allocation (what a multi-GPU host gathers with one collective)."""
+    import torch
+    B = 5000
+    x0 = W.random_offsets_x0(B, 3)
+    with BatchedMPC(4, 1, 30, B) as eng:
+        eng.set_model(W.bicycle4_model())
+        u0, it, st = eng.solve(x0)
+        view, off_it, off_st = eng.device_results_block()
+        blk = torch.as_tensor(view, device="cuda").cpu().numpy()
+        assert off_it % 256 == 0 and off_st % 256 == 0 and off_it >= 8 * B and off_st >= off_it + 4 * B and blk.size >= off_st + B
+        assert np.array_equal(blk[: 8 * B].view(np.float64), u0[:, 0])
+        assert np.array_equal(blk[off_it: off_it + 4 * B].view(np.uint32), it)
+        assert np.array_equal(blk[off_st: off_st + B], st)
+        du, di, ds = eng.device_results()
+        assert np.array_equal(torch.as_tensor(di, device="cuda").cpu().numpy().view(np.uint32), it)
+
+
 def test_error_paths_on_device():
     from trajectory_controller_b200.engine import BmpcError
     with BatchedMPC(4, 1, 10, 8) as eng:

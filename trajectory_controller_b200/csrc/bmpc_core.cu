@@ -37,7 +37,7 @@ cudaError_t DevBuf::alloc_zero(size_t n, cudaStream_t st)
 }
 void DevBuf::release()
 {
-    if (p) cudaFree(p);
+    if (p && !view) cudaFree(p);
     p = nullptr; bytes = 0;
 }
 
@@ -206,9 +206,17 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     chk(cudaEventCreate(&h->ev_mid), "cudaEventCreate");
     const size_t c = (size_t)capacity, es = (size_t)h->elem;
     chk(h->x0.alloc_zero(c * S * es, h->stream), "alloc x0");
-    chk(h->u0.alloc_zero(c * I * es, h->stream), "alloc u0");
-    chk(h->iters.alloc_zero(c * 4, h->stream), "alloc iters");
-    chk(h->status.alloc_zero(c, h->stream), "alloc status");
+    {   // the results of a solve live in one allocation, so that a multi-GPU host gathers them with ONE collective
+        // and one copy (bmpc_device_results_block)
+        auto up = [](size_t n) { return (n + 255) & ~(size_t)255; };
+        const size_t o_it = up(c * I * es), o_st = o_it + up(c * 4), total = o_st + up(c);
+        chk(h->results.alloc_zero(total, h->stream), "alloc results");
+        if (h->results.p) {
+            h->u0.p = h->results.p; h->u0.bytes = c * I * es; h->u0.view = true;
+            h->iters.p = (char*)h->results.p + o_it; h->iters.bytes = c * 4; h->iters.view = true;
+            h->status.p = (char*)h->results.p + o_st; h->status.bytes = c; h->status.view = true;
+        }
+    }
     chk(h->controls.alloc_zero(c * h->NI * es, h->stream), "alloc controls");
     chk(h->vstate.alloc_zero(c * h->NI * es, h->stream), "alloc v");
     chk(h->target_const.alloc_zero(c * S * es, h->stream), "alloc target");
@@ -251,7 +259,7 @@ void bmpc_destroy(bmpc_t* h)
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->u0,
+    DevBuf* bufs[] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi, &h->mlambda, &h->mqdiag, &h->x0, &h->results, &h->u0,
                       &h->iters, &h->status, &h->controls, &h->vstate, &h->target_const, &h->target_full, &h->queue,
                       &h->pg_list, &h->park, &h->park_iter, &h->c_list, &h->c_park, &h->c_iter, &h->stage, &h->small, &h->cl_path, &h->cl_pose, &h->cl_tgt, &h->cl_idx, &h->cl_itot, &h->cl_imax};
     for (DevBuf* b : bufs) b->release();

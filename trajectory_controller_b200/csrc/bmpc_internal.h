@@ -26,6 +26,7 @@ int fail_cuda(cudaError_t e, const char* what);
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    bool view = false;            // a window into another DevBuf's allocation: never freed, never grown
     cudaError_t reserve(size_t n);
     cudaError_t alloc_zero(size_t n, cudaStream_t st);
     void release();
@@ -98,6 +99,7 @@ struct bmpc_handle {
     bmpc::DevBuf mA, mB, mC, mQ, mR, mlo, mhi, mlambda, mqdiag;  // SoA [elem][cap]
 
     // state
+    bmpc::DevBuf results;         // ONE allocation: u0 | iters | status (each 256-byte aligned) — u0 / iters / status below are views
     bmpc::DevBuf x0, u0, iters, status, controls, vstate, target_const, target_full, queue;
     bmpc::DevBuf pg_list, park, park_iter;   // split solve: hand-over ring and the by-slot state of parked instances (pg_kernel.cuh)
     bool ring_dirty = true;          // pg_list may hold entries of an earlier launch (bmpc_solve_resident_async)

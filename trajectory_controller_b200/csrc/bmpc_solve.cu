@@ -367,6 +367,16 @@ int bmpc_device_results(bmpc_t* h, void** u0, void** iters, void** status)
     return BMPC_OK;
 }
 
+int bmpc_device_results_block(bmpc_t* h, void** base, uint64_t* bytes, uint64_t* iters_offset, uint64_t* status_offset)
+{
+    if (!h) return fail(BMPC_E_INVALID, "bmpc_device_results_block: null handle");
+    if (base) *base = h->results.p;
+    if (bytes) *bytes = h->results.bytes;
+    if (iters_offset) *iters_offset = (uint64_t)((char*)h->iters.p - (char*)h->results.p);
+    if (status_offset) *status_offset = (uint64_t)((char*)h->status.p - (char*)h->results.p);
+    return BMPC_OK;
+}
+
 int bmpc_last_kernel_ms(bmpc_t* h, float* ms)
 {
     if (!h || !ms) return fail(BMPC_E_INVALID, "bmpc_last_kernel_ms: null argument");

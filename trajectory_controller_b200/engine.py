@@ -58,6 +58,7 @@ SIGNATURES = {
     "bmpc_download": (C.c_int, [C.c_void_p, C.c_int64, _dp, _u32p, _u8p]),
     "bmpc_sync": (C.c_int, [C.c_void_p]),
     "bmpc_device_results": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 3),
+    "bmpc_device_results_block": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)] + [C.POINTER(C.c_uint64)] * 3),
     "bmpc_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bmpc_last_kernel_ms": (C.c_int, [C.c_void_p, _fp]),
     "bmpc_last_stage_ms": (C.c_int, [C.c_void_p, _fp, _fp]),
@@ -326,6 +327,13 @@ class BatchedMPC:
         return (_DeviceView(ptrs[0].value, (self.I, self.capacity), ft),
                 _DeviceView(ptrs[1].value, (self.capacity,), "<i4"),
                 _DeviceView(ptrs[2].value, (self.capacity,), "|u1"))
+
+    def device_results_block(self):
+        """(device view of the whole result block as uint8 [bytes], iters_offset, status_offset): u0 | iters | status in
+        one allocation — one collective gathers a rank's results."""
+        base = C.c_void_p(); n, oi, os_ = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        _check(lib().bmpc_device_results_block(self._h, C.byref(base), C.byref(n), C.byref(oi), C.byref(os_)))
+        return _DeviceView(base.value, (n.value,), "|u1"), oi.value, os_.value
 
     def set_stream(self, cuda_stream: int | None):
         """Borrow a caller's cudaStream_t (integer handle, e.g. torch.cuda.current_stream().cuda_stream); None/0 = own."""
