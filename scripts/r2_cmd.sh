@@ -1,3 +1,4 @@
-timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -4 gpurun_out/pytest_gpu.log
-bash scripts/r2_scale.sh 2
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+for N in 30 60 100; do
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:pair_kernel -s 1 -c 1 -o gpurun_out/pair_pim_N$N -f python scripts/sweep_probe.py $N 256 > gpurun_out/ncu_pair_N$N.log 2>&1; tail -1 gpurun_out/ncu_pair_N$N.log
+done

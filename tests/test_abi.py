@@ -64,6 +64,23 @@ def test_no_cpu_fallback_without_device(engine_lib):
     assert e.value.code == -3 and "no CPU fallback" in str(e.value)
 
 
+def test_group_create_rejects_bad_arguments(engine_lib):
+    """Device groups: argument errors and the loud no-device failure need no GPU."""
+    L = engine_lib.lib()
+    g = C.c_void_p()
+    assert L.bmpc_group_create(None, 4, 1, 30, 64, 64, 0, None, 0, 0) == -1
+    assert L.bmpc_group_create(C.byref(g), 4, 1, 30, 64, 64, 0, None, 0, 7) == -1          # unknown assignment
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if not has_gpu:
+        assert L.bmpc_group_create(C.byref(g), 4, 1, 30, 64, 64, 0, None, 0, 0) == -3
+        assert b"no CPU fallback" in L.bmpc_last_error()
+    assert L.bmpc_group_size(None) == 0 and L.bmpc_group_member(None, 0) is None
+
+
 def test_product_never_imports_oracle():
     """Nothing under trajectory_controller_b200/ may reference oracle/ (SURVEY.md §8(c) rule)."""
     pkg = os.path.join(ROOT, "trajectory_controller_b200")
