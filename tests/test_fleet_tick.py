@@ -87,6 +87,34 @@ def test_fleet_tick_matches_restatement(oracle, B, use_lookup):
     assert np.all(np.abs(got["steering_front"]) <= 22 * np.pi / 180 + 1e-15)
 
 
+@pytest.mark.parametrize("layout", ["pb", "bp"])
+def test_chunked_tick_equals_one_chunk(layout, monkeypatch):
+    """A large tick is cut into 4 chunks whose uploads overlap the kernels of the chunk before (bmpc_fleet_tick_tobi);
+    the cut must be invisible: every output bit-equal to the one-chunk tick, incl. ragged polylines, the device-side
+    look-ups and the crossing PID state carried over two ticks."""
+    from trajectory_controller_b200.engine import LOOKUP_DISTANCE, LOOKUP_VELOCITY, PID_SLOWDOWN, BatchedMPC
+    B, P, N = 3001, 48, 4
+    px, py, dx, dy, vel, speed, dist, _ = _stop_fleet(B, P, 31)
+    npts = np.random.default_rng(4).integers(0, P + 1, B).astype(np.int32)
+    arrs = [px, py, dx, dy, vel] if layout == "pb" else [np.ascontiguousarray(a.T) for a in (px, py, dx, dy, vel)]
+    res = {}
+    for mode, chunk_min in (("one", "1000000"), ("four", "1")):
+        monkeypatch.setenv("BMPC_TICK_CHUNK_MIN", chunk_min)
+        with BatchedMPC(2, 2, N, B) as eng:
+            eng.set_lookup(LOOKUP_DISTANCE, [0.0, 1.0, 4.0], [0.4, 0.7, 1.6])
+            eng.set_lookup(LOOKUP_VELOCITY, [0.0, 2.0, 5.0], [0.3, 2.0, 3.5])
+            eng.set_pid(PID_SLOWDOWN, 1.0, 0.3, 0.05, 0.01)
+            a = eng.fleet_tick_tobi(speed, None, *arrs, layout=layout, npoints=npts)      # look-ahead + velocity on the device
+            b = eng.fleet_tick_tobi(speed, dist, *arrs, layout=layout, npoints=npts)      # second tick: PID state carried over
+            res[mode] = (a, b, eng.get_pid(PID_SLOWDOWN, B))
+    for t in (0, 1):
+        for k, v in res["one"][t].items():
+            w = res["four"][t][k]
+            assert np.array_equal(v.view(np.uint8), w.view(np.uint8)), (layout, t, k)
+    for v, w in zip(res["one"][2], res["four"][2]):
+        assert np.array_equal(v.view(np.uint8), w.view(np.uint8))
+
+
 def test_fleet_tick_rejects_wrong_shape():
     from trajectory_controller_b200.engine import BatchedMPC, BmpcError
     z = np.zeros((4, 3), dtype=np.float32)

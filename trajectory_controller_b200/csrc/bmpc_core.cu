@@ -271,6 +271,8 @@ void bmpc_destroy(bmpc_t* h)
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_mid) cudaEventDestroy(h->ev_mid);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    for (cudaEvent_t e : h->ev_chunk) if (e) cudaEventDestroy(e);
     delete h;
 }
 

@@ -66,6 +66,10 @@ __host__ __device__ inline size_t small_results_err_offset(int count, int I) { r
 cudaError_t pack_results(const void* u0, const uint32_t* iters, const uint8_t* status, const unsigned long long* queue, int count,
                          int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st);
 
+// bmpc_solve_resident_async on the instances [first, first + count) of the handle (cold solves with one target per
+// instance only: the fleet tick's chunks).
+int solve_range_async(bmpc_handle* h, long long first, long long count, unsigned flags);
+
 const ShapeOps* find_shape(int S, int I, int N);
 const ShapeOps* select_pattern(int S, int I, int N, const double* A, const double* B, const double* C, const double* Q,
                                long long count, bool as_float);
@@ -81,6 +85,8 @@ struct bmpc_handle {
     const bmpc::ShapeOps* solve_ops;   // pattern-specialised unit chosen by bmpc_set_model for the current model
     cudaStream_t stream = nullptr;       // the stream calls run on (own_stream unless bmpc_set_stream borrowed one)
     cudaStream_t own_stream = nullptr;
+    cudaStream_t copy_stream = nullptr;  // fleet tick: uploads of the next chunk while this one computes
+    cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr;   // solve start / end / between stage A and stage B
     bool timed_split = false;
     bool timed = false;

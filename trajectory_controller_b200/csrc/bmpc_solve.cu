@@ -182,9 +182,17 @@ int bmpc_upload_x0(bmpc_t* h, int64_t count, const double* x0)
 int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
 {
     if (!h) return fail(BMPC_E_INVALID, "bmpc_solve: null handle");
+    return bmpc::solve_range_async(h, 0, count, flags);
+}
+
+}  // extern "C"
+
+int bmpc::solve_range_async(bmpc_handle* h, long long first, long long count, unsigned flags)
+{
     if (!h->have_model) return fail(BMPC_E_STATE, "bmpc_solve: bmpc_set_model has not been called");
-    if (count < 1 || count > h->cap) return fail(BMPC_E_INVALID, "bmpc_solve: count out of capacity");
-    if (h->per_instance && count > h->model_count) return fail(BMPC_E_INVALID, "bmpc_solve: more instances than per-instance models");
+    if (first < 0 || count < 1 || first + count > h->cap) return fail(BMPC_E_INVALID, "bmpc_solve: count out of capacity");
+    if (h->per_instance && first + count > h->model_count) return fail(BMPC_E_INVALID, "bmpc_solve: more instances than per-instance models");
+    if (first != 0 && ((flags & BMPC_WARM) || h->full_targets)) return fail(BMPC_E_INVALID, "bmpc_solve: a sub-range solve must be cold with one target per instance");
     BMPC_CUDA(cudaSetDevice(h->device));
     const bool warm = (flags & BMPC_WARM) != 0;
     GenericSolve g{};
@@ -193,7 +201,7 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     g.eps = h->eps; g.max_iter = h->max_iter;
     g.warm = warm; g.keep_controls = warm || (flags & BMPC_KEEP_CONTROLS);
     g.target_full = h->full_targets; g.head = h->head;
-    g.count = count; g.stride = h->cap;
+    g.count = count; g.stride = h->cap; g.first = first;
     g.x0 = h->x0.p; g.controls = h->controls.p; g.vstate = h->vstate.p;
     g.target = h->full_targets ? h->target_full.p : h->target_const.p;
     g.u0 = h->u0.p; g.iters = (uint32_t*)h->iters.p; g.status = (uint8_t*)h->status.p;
@@ -288,6 +296,8 @@ int bmpc_solve_resident_async(bmpc_t* h, int64_t count, unsigned flags)
     }
     return BMPC_OK;
 }
+
+extern "C" {
 
 int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t* status)
 {

@@ -15,6 +15,7 @@ struct GenericSolve {
     uint32_t max_iter;
     int warm, keep_controls, target_full, head;
     long long count, stride;
+    long long first;                             // the launch works on instances [first, first + count) of the handle
     const void* x0; void* controls; void* vstate; void* target; void* u0;
     uint32_t* iters; uint8_t* status;
     const void *mA, *mB, *mC, *mQ, *mR, *mlo, *mhi, *mlambda, *mqdiag;

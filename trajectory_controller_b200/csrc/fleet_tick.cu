@@ -14,6 +14,8 @@
 // functions that cannot be made bit-identical to the reference's host are atan2 / atan2f (CUDA's, <= 2 ulp, against
 // glibc's): see bmpc.h.  PID / LookupTable semantics: include/bmpc.h (sensor_utils, lms_math are not vendored).
 #include <cmath>
+#include <cstdlib>
+#include <string>
 
 #include "bmpc_internal.h"
 
@@ -198,59 +200,121 @@ inline PidGains gains_of(const bmpc_t* h, int which) { return PidGains{h->pid_ga
 
 // The front end both branches share: uploads, look-ahead, getTrajectoryPoint, crossing clamp.  Device results:
 // ex[7] idx, ex[8] flag, ex[9..13] the trajectory point (x, y, dir x, dir y, velocity), ex[14] car velocity (float).
-int fleet_front(bmpc_t* h, const char* who, int64_t count, const float* velocity, const float* dist, int P,
-                const int32_t* npoints, const float* px, const float* py, const float* dx, const float* dy, const float* vel,
-                int64_t stride_instance, int64_t stride_point)
+// It works on the vehicles [b0, b0 + n) of a tick of `count`: a large tick is cut into chunks whose uploads (on the
+// handle's copy stream) overlap the kernels of the chunk before (fleet_chunks).
+struct FrontArgs {
+    int64_t count; const float* velocity; const float* dist; int P; const int32_t* npoints;
+    const float *px, *py, *dx, *dy, *vel; int64_t si, sp;
+};
+
+int fleet_check(bmpc_t* h, const char* who, const FrontArgs& a)
 {
-    if (count < 1 || count > h->cap || P < 0) return fail(BMPC_E_INVALID, std::string(who) + ": count / P out of range");
-    if (P > 0 && (!px || !py || !dx || !dy || !vel)) return fail(BMPC_E_INVALID, std::string(who) + ": null trajectory array");
-    if (stride_instance < 0 || stride_point < 0) return fail(BMPC_E_INVALID, std::string(who) + ": negative stride");
-    if (!dist && !h->foh && h->lut_n[BMPC_LOOKUP_DISTANCE] <= 0)
+    if (a.count < 1 || a.count > h->cap || a.P < 0) return fail(BMPC_E_INVALID, std::string(who) + ": count / P out of range");
+    if (a.P > 0 && (!a.px || !a.py || !a.dx || !a.dy || !a.vel)) return fail(BMPC_E_INVALID, std::string(who) + ": null trajectory array");
+    if (a.si < 0 || a.sp < 0) return fail(BMPC_E_INVALID, std::string(who) + ": negative stride");
+    if (!a.dist && !h->foh && h->lut_n[BMPC_LOOKUP_DISTANCE] <= 0)
         return fail(BMPC_E_STATE, std::string(who) + ": dist == NULL needs the BMPC_LOOKUP_DISTANCE table (bmpc_set_lookup) or FOH drive mode");
-    BMPC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = h->stream;
-    const size_t c = (size_t)count;
-    const size_t nflt = P > 0 ? (size_t)((count - 1) * stride_instance + (int64_t)(P - 1) * stride_point + 1) : 0;
-    const float* src[5] = {px, py, dx, dy, vel};
-    for (int a = 0; a < 5; ++a) {
-        BMPC_CUDA(h->ex[a].reserve(nflt * 4 + 4));
-        if (nflt) BMPC_CUDA(cudaMemcpyAsync(h->ex[a].p, src[a], nflt * 4, cudaMemcpyHostToDevice, st));
-    }
+    return BMPC_OK;
+}
+
+// Device buffers of a tick (sized for all `count` vehicles, same layout as the host arrays).
+int fleet_reserve(bmpc_t* h, const FrontArgs& a)
+{
+    const size_t c = (size_t)a.count;
+    const size_t nflt = a.P > 0 ? (size_t)((a.count - 1) * a.si + (int64_t)(a.P - 1) * a.sp + 1) : 0;
+    for (int k = 0; k < 5; ++k) BMPC_CUDA(h->ex[k].reserve(nflt * 4 + 4));
     const size_t voff = ((c * 4 + 7) / 8) * 8;
     BMPC_CUDA(h->ex[14].reserve(voff + c * 8));                           // velocity (float) | v_model (double)
-    BMPC_CUDA(cudaMemcpyAsync(h->ex[14].p, velocity, c * 4, cudaMemcpyHostToDevice, st));
     BMPC_CUDA(h->ex[5].reserve(c * 4));
-    if (dist) BMPC_CUDA(cudaMemcpyAsync(h->ex[5].p, dist, c * 4, cudaMemcpyHostToDevice, st));
-    else {                                                                // :66 / :70-73 on the device
-        k_lookahead<<<grid_for(count, 256), 256, 0, st>>>(count, (const float*)h->ex[14].p, (const float*)h->lut[BMPC_LOOKUP_DISTANCE].p,
-                                                          h->lut_n[BMPC_LOOKUP_DISTANCE], h->foh ? 1 : 0, h->foh_min, h->foh_slope, (float*)h->ex[5].p);
+    if (a.npoints) BMPC_CUDA(h->ex[6].reserve(c * 4));
+    for (int k = 7; k < 14; ++k) BMPC_CUDA(h->ex[k].reserve(c * 4));
+    return BMPC_OK;
+}
+
+// How a tick is cut: 4 chunks when it is large and the polylines are point-major ([P][count], a chunk is P rows of a 2-D
+// copy) or instance-major ([count][P], a chunk is contiguous); one chunk otherwise.  BMPC_TICK_CHUNK_MIN: developer
+// override of the size from which ticks are chunked (tests).
+int fleet_chunks(const FrontArgs& a)
+{
+    const char* e = std::getenv("BMPC_TICK_CHUNK_MIN");
+    const long long min_count = e ? std::atoll(e) : 32768ll;
+    if (a.count < min_count || a.P <= 0) return 1;
+    const bool point_major = a.si == 1 && a.sp >= a.count;
+    const bool instance_major = a.sp == 1 && a.si >= a.P;
+    return (point_major || instance_major) ? 4 : 1;
+}
+
+// Uploads of the vehicles [b0, b0 + n) on stream `st`.
+int fleet_upload(bmpc_t* h, const FrontArgs& a, int64_t b0, int64_t n, const double* v_model, cudaStream_t st)
+{
+    const float* src[5] = {a.px, a.py, a.dx, a.dy, a.vel};
+    if (a.P > 0) {
+        if (b0 == 0 && n == a.count) {                                    // whole tick: one flat copy per array
+            const size_t nflt = (size_t)((a.count - 1) * a.si + (int64_t)(a.P - 1) * a.sp + 1);
+            for (int k = 0; k < 5; ++k) BMPC_CUDA(cudaMemcpyAsync(h->ex[k].p, src[k], nflt * 4, cudaMemcpyHostToDevice, st));
+        } else if (a.si == 1) {                                           // point-major: P rows of n floats, pitch sp
+            for (int k = 0; k < 5; ++k)
+                BMPC_CUDA(cudaMemcpy2DAsync((float*)h->ex[k].p + b0, (size_t)a.sp * 4, src[k] + b0, (size_t)a.sp * 4, (size_t)n * 4,
+                                            (size_t)a.P, cudaMemcpyHostToDevice, st));
+        } else {                                                          // instance-major: n polylines of pitch si
+            const size_t nflt = (size_t)((n - 1) * a.si + a.P);
+            for (int k = 0; k < 5; ++k)
+                BMPC_CUDA(cudaMemcpyAsync((float*)h->ex[k].p + b0 * a.si, src[k] + b0 * a.si, nflt * 4, cudaMemcpyHostToDevice, st));
+        }
+    }
+    BMPC_CUDA(cudaMemcpyAsync((float*)h->ex[14].p + b0, a.velocity + b0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (a.dist) BMPC_CUDA(cudaMemcpyAsync((float*)h->ex[5].p + b0, a.dist + b0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (a.npoints) BMPC_CUDA(cudaMemcpyAsync((int32_t*)h->ex[6].p + b0, a.npoints + b0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (v_model) {
+        const size_t voff = (((size_t)a.count * 4 + 7) / 8) * 8;
+        BMPC_CUDA(cudaMemcpyAsync((double*)((char*)h->ex[14].p + voff) + b0, v_model + b0, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    }
+    return BMPC_OK;
+}
+
+// Look-ahead, getTrajectoryPoint and the crossing clamp for the vehicles [b0, b0 + n) on stream `st`.
+int fleet_front_kernels(bmpc_t* h, const FrontArgs& a, int64_t b0, int64_t n, cudaStream_t st)
+{
+    if (!a.dist) {                                                        // :66 / :70-73 on the device
+        k_lookahead<<<grid_for(n, 256), 256, 0, st>>>(n, (const float*)h->ex[14].p + b0, (const float*)h->lut[BMPC_LOOKUP_DISTANCE].p,
+                                                      h->lut_n[BMPC_LOOKUP_DISTANCE], h->foh ? 1 : 0, h->foh_min, h->foh_slope,
+                                                      (float*)h->ex[5].p + b0);
         BMPC_CUDA(cudaGetLastError());
         h->launches++;
     }
-    if (npoints) {
-        BMPC_CUDA(h->ex[6].reserve(c * 4));
-        BMPC_CUDA(cudaMemcpyAsync(h->ex[6].p, npoints, c * 4, cudaMemcpyHostToDevice, st));
-    }
-    for (int a = 7; a < 14; ++a) BMPC_CUDA(h->ex[a].reserve(c * 4));
-    const int32_t* d_np = npoints ? (const int32_t*)h->ex[6].p : nullptr;
-    BMPC_CUDA(launch_extract(count, P, d_np, (const float*)h->ex[0].p, (const float*)h->ex[1].p, (const float*)h->ex[2].p,
-                             (const float*)h->ex[3].p, (const float*)h->ex[4].p, stride_instance, stride_point,
-                             (const float*)h->ex[5].p, (int32_t*)h->ex[7].p, (uint8_t*)h->ex[8].p, (float*)h->ex[9].p,
-                             (float*)h->ex[10].p, (float*)h->ex[11].p, (float*)h->ex[12].p, (float*)h->ex[13].p, st));
+    const int32_t* d_np = a.npoints ? (const int32_t*)h->ex[6].p + b0 : nullptr;
+    const int64_t o = b0 * a.si;
+    BMPC_CUDA(launch_extract(n, a.P, d_np, (const float*)h->ex[0].p + o, (const float*)h->ex[1].p + o, (const float*)h->ex[2].p + o,
+                             (const float*)h->ex[3].p + o, (const float*)h->ex[4].p + o, a.si, a.sp,
+                             (const float*)h->ex[5].p + b0, (int32_t*)h->ex[7].p + b0, (uint8_t*)h->ex[8].p + b0, (float*)h->ex[9].p + b0,
+                             (float*)h->ex[10].p + b0, (float*)h->ex[11].p + b0, (float*)h->ex[12].p + b0, (float*)h->ex[13].p + b0, st));
     h->launches++;
-    if (h->crossing_on && P > 0) {                                        // :445-473
-        int rc = pid_state_ready(h, BMPC_PID_SLOWDOWN);
-        if (rc) return rc;
+    if (h->crossing_on && a.P > 0) {                                      // :445-473
         float* in = (float*)h->pid_state[BMPC_PID_SLOWDOWN].p;
         const size_t cap = (size_t)h->cap;
-        k_crossing<<<grid_for(count, 128), 128, 0, st>>>(count, P, d_np, (const float*)h->ex[0].p, (const float*)h->ex[1].p,
-                                                         (const float*)h->ex[4].p, stride_instance, stride_point, h->crossing,
-                                                         gains_of(h, BMPC_PID_SLOWDOWN), in, in + cap, (uint8_t*)(in + 2 * cap),
-                                                         (float*)h->ex[13].p);
+        k_crossing<<<grid_for(n, 128), 128, 0, st>>>(n, a.P, d_np, (const float*)h->ex[0].p + o, (const float*)h->ex[1].p + o,
+                                                     (const float*)h->ex[4].p + o, a.si, a.sp, h->crossing,
+                                                     gains_of(h, BMPC_PID_SLOWDOWN), in + b0, in + cap + b0, (uint8_t*)(in + 2 * cap) + b0,
+                                                     (float*)h->ex[13].p + b0);
         BMPC_CUDA(cudaGetLastError());
         h->launches++;
     }
     return BMPC_OK;
+}
+
+// One-chunk front end (the PID branch and small ticks).
+int fleet_front(bmpc_t* h, const char* who, int64_t count, const float* velocity, const float* dist, int P,
+                const int32_t* npoints, const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                int64_t stride_instance, int64_t stride_point)
+{
+    const FrontArgs a{count, velocity, dist, P, npoints, px, py, dx, dy, vel, stride_instance, stride_point};
+    int rc = fleet_check(h, who, a);
+    if (rc) return rc;
+    BMPC_CUDA(cudaSetDevice(h->device));
+    if ((rc = fleet_reserve(h, a))) return rc;
+    if (h->crossing_on && P > 0 && (rc = pid_state_ready(h, BMPC_PID_SLOWDOWN))) return rc;
+    if ((rc = fleet_upload(h, a, 0, count, nullptr, h->stream))) return rc;
+    return fleet_front_kernels(h, a, 0, count, h->stream);
 }
 
 }  // namespace
@@ -389,80 +453,111 @@ int bmpc_fleet_tick_tobi(bmpc_t* h, int64_t count, const bmpc_tick_config* cfg, 
     if (!h || !cfg || !velocity || !steering_front || !steering_rear || !target_speed || !target_distance || !state)
         return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: null argument");
     if (h->S != 2 || h->I != 2) return fail(BMPC_E_INVALID, "bmpc_fleet_tick_tobi: the handle must be a (2,2,N) controller (mpcControllerTobi, src/...:303-366)");
-    int rc = fleet_front(h, "bmpc_fleet_tick_tobi", count, velocity, dist, P, npoints, px, py, dx, dy, vel, stride_instance, stride_point);
+    const FrontArgs fa{count, velocity, dist, P, npoints, px, py, dx, dy, vel, stride_instance, stride_point};
+    int rc = fleet_check(h, "bmpc_fleet_tick_tobi", fa);
     if (rc) return rc;
+    BMPC_CUDA(cudaSetDevice(h->device));
+    if ((rc = fleet_reserve(h, fa))) return rc;
+    if (h->crossing_on && P > 0 && (rc = pid_state_ready(h, BMPC_PID_SLOWDOWN))) return rc;
     cudaStream_t st = h->stream;
     const size_t c = (size_t)count, es = (size_t)h->elem, cap = (size_t)h->cap;
 
-    // ---- per-vehicle model, target and zero state ---------------------------------------------------------------------
+    // ---- buffers: per-vehicle model, target debug rows, outputs --------------------------------------------------------
     const size_t voff = ((c * 4 + 7) / 8) * 8;
     BMPC_CUDA(h->ex[15].reserve(cap * 8 * 2 + c * (8 + 8 + 4 + 4 + 1)));   // tgt_dbg [2][cap] | outputs
-    double* d_vmodel = nullptr;
-    if (v_model) {
-        d_vmodel = (double*)((char*)h->ex[14].p + voff);
-        BMPC_CUDA(cudaMemcpyAsync(d_vmodel, v_model, c * 8, cudaMemcpyHostToDevice, st));
-    }
+    double* d_vmodel = v_model ? (double*)((char*)h->ex[14].p + voff) : nullptr;
     DevBuf* mb[7] = {&h->mA, &h->mB, &h->mC, &h->mQ, &h->mR, &h->mlo, &h->mhi};
     const int mlen[7] = {4, 4, 2, 2, 2, 2, 2};
     for (int a = 0; a < 7; ++a) BMPC_CUDA(mb[a]->reserve(cap * mlen[a] * es));
     BMPC_CUDA(h->mlambda.reserve(cap * es));
     BMPC_CUDA(h->mqdiag.reserve(cap * h->NI * es));
-    TickParams q{};
-    q.count = count; q.stride = h->cap; q.T = cfg->T; q.l = cfg->l; q.w_y = cfg->weight_y; q.w_phi = cfg->weight_phi;
-    q.w_sf = cfg->weight_steering_front; q.w_sr = cfg->weight_steering_rear; q.alpha_max = cfg->alpha_max;
-    q.velocity = (const float*)h->ex[14].p; q.v_model = d_vmodel;
-    q.vtable = (const float*)h->lut[BMPC_LOOKUP_VELOCITY].p; q.vn = h->lut_n[BMPC_LOOKUP_VELOCITY];
-    q.opx = (const float*)h->ex[9].p; q.opy = (const float*)h->ex[10].p; q.odx = (const float*)h->ex[11].p; q.ody = (const float*)h->ex[12].p;
+    if (target) BMPC_CUDA(h->stage.reserve(c * 2 * 8));
     double* tgt_dbg = (double*)h->ex[15].p;
-    const unsigned grid = (unsigned)((count + 127) / 128);
-    if (h->elem == 8)
-        k_tick_prepare<double><<<grid, 128, 0, st>>>(q, (double*)h->mA.p, (double*)h->mB.p, (double*)h->mC.p, (double*)h->mQ.p,
-                                                     (double*)h->mR.p, (double*)h->mlo.p, (double*)h->mhi.p, (double*)h->x0.p,
-                                                     (double*)h->target_const.p, tgt_dbg);
-    else
-        k_tick_prepare<float><<<grid, 128, 0, st>>>(q, (float*)h->mA.p, (float*)h->mB.p, (float*)h->mC.p, (float*)h->mQ.p,
-                                                    (float*)h->mR.p, (float*)h->mlo.p, (float*)h->mhi.p, (float*)h->x0.p,
-                                                    (float*)h->target_const.p, tgt_dbg);
-    BMPC_CUDA(cudaGetLastError());
-    h->launches++;
-
-    // ---- fresh controllers: constructor recursion (mpc.h:114-123), then one cold operator() each ------------------------
-    GenericCtor g{count, h->cap, h->mA.p, h->mB.p, h->mQ.p, h->mR.p, h->mlambda.p, h->mqdiag.p};
-    BMPC_CUDA(h->ops->ctor(h->precision, h->mode, g, st));
-    h->launches++;
-    h->per_instance = true; h->model_count = count; h->have_model = true;
-    h->full_targets = false; h->head = 0;                         // set_target(val): one target for all horizon steps
-    const ShapeOps* tobi = h->specialize ? find_pattern(h->S, h->I, h->N, "tobi") : nullptr;   // holds by construction
-    h->solve_ops = tobi ? tobi : h->ops;
-    rc = bmpc_solve_resident_async(h, count, 0);
-    if (rc) return rc;
-
-    // ---- CarCommand fields ----------------------------------------------------------------------------------------------
     char* ob = (char*)h->ex[15].p + cap * 8 * 2;
     double* d_sf = (double*)ob; double* d_sr = d_sf + c;
     float* d_ts = (float*)(d_sr + c); float* d_td = d_ts + c;
     uint8_t* d_state = (uint8_t*)(d_td + c);
-    if (h->elem == 8)
-        k_tick_finish<double><<<grid, 128, 0, st>>>(count, h->cap, (const double*)h->u0.p, (const float*)h->ex[9].p,
-                                                    (const float*)h->ex[10].p, (const float*)h->ex[13].p, d_sf, d_sr, d_ts, d_td, d_state);
-    else
-        k_tick_finish<float><<<grid, 128, 0, st>>>(count, h->cap, (const float*)h->u0.p, (const float*)h->ex[9].p,
-                                                   (const float*)h->ex[10].p, (const float*)h->ex[13].p, d_sf, d_sr, d_ts, d_td, d_state);
-    BMPC_CUDA(cudaGetLastError());
-    h->launches++;
-    BMPC_CUDA(cudaMemcpyAsync(steering_front, d_sf, c * 8, cudaMemcpyDeviceToHost, st));
-    BMPC_CUDA(cudaMemcpyAsync(steering_rear, d_sr, c * 8, cudaMemcpyDeviceToHost, st));
-    BMPC_CUDA(cudaMemcpyAsync(target_speed, d_ts, c * 4, cudaMemcpyDeviceToHost, st));
-    BMPC_CUDA(cudaMemcpyAsync(target_distance, d_td, c * 4, cudaMemcpyDeviceToHost, st));
-    BMPC_CUDA(cudaMemcpyAsync(state, d_state, c, cudaMemcpyDeviceToHost, st));
-    if (idx) BMPC_CUDA(cudaMemcpyAsync(idx, h->ex[7].p, c * 4, cudaMemcpyDeviceToHost, st));
-    if (flag) BMPC_CUDA(cudaMemcpyAsync(flag, h->ex[8].p, c, cudaMemcpyDeviceToHost, st));
-    if (iters) BMPC_CUDA(cudaMemcpyAsync(iters, h->iters.p, c * 4, cudaMemcpyDeviceToHost, st));
-    if (target) {                                                  // [count][2] = y_soll, phi_soll
-        BMPC_CUDA(h->stage.reserve(c * 2 * 8));
-        BMPC_CUDA(soa_to_aos(tgt_dbg, (double*)h->stage.p, count, 2, h->cap, 8, st));
+    h->per_instance = true; h->model_count = count; h->have_model = true;
+    h->full_targets = false; h->head = 0;                         // set_target(val): one target for all horizon steps
+    const ShapeOps* tobi = h->specialize ? find_pattern(h->S, h->I, h->N, "tobi") : nullptr;   // holds by construction
+    h->solve_ops = tobi ? tobi : h->ops;
+
+    // ---- chunks: the uploads of chunk k+1 (copy stream) overlap the kernels and the downloads of chunk k ------------------
+    const int chunks = fleet_chunks(fa);
+    if (chunks > 1 && !h->copy_stream) {
+        BMPC_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 8; ++k) BMPC_CUDA(cudaEventCreateWithFlags(&h->ev_chunk[k], cudaEventDisableTiming));
+    }
+    auto range = [&](int k, int64_t* b0, int64_t* n) { *b0 = count * k / chunks; *n = count * (k + 1) / chunks - *b0; };
+    if (chunks > 1) {
+        // the copy stream starts after whatever the handle's stream still has queued on these buffers
+        BMPC_CUDA(cudaEventRecord(h->ev_chunk[7], st));
+        BMPC_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_chunk[7], 0));
+        for (int k = 0; k < chunks; ++k) {
+            int64_t b0, n; range(k, &b0, &n);
+            if ((rc = fleet_upload(h, fa, b0, n, v_model, h->copy_stream))) return rc;
+            BMPC_CUDA(cudaEventRecord(h->ev_chunk[k], h->copy_stream));
+        }
+    } else if ((rc = fleet_upload(h, fa, 0, count, v_model, st))) return rc;
+
+    for (int k = 0; k < chunks; ++k) {
+        int64_t b0, n; range(k, &b0, &n);
+        if (n <= 0) continue;
+        if (chunks > 1) BMPC_CUDA(cudaStreamWaitEvent(st, h->ev_chunk[k], 0));
+        if ((rc = fleet_front_kernels(h, fa, b0, n, st))) return rc;
+        // ---- per-vehicle model, target and zero state
+        TickParams q{};
+        q.count = n; q.stride = h->cap; q.T = cfg->T; q.l = cfg->l; q.w_y = cfg->weight_y; q.w_phi = cfg->weight_phi;
+        q.w_sf = cfg->weight_steering_front; q.w_sr = cfg->weight_steering_rear; q.alpha_max = cfg->alpha_max;
+        q.velocity = (const float*)h->ex[14].p + b0; q.v_model = d_vmodel ? d_vmodel + b0 : nullptr;
+        q.vtable = (const float*)h->lut[BMPC_LOOKUP_VELOCITY].p; q.vn = h->lut_n[BMPC_LOOKUP_VELOCITY];
+        q.opx = (const float*)h->ex[9].p + b0; q.opy = (const float*)h->ex[10].p + b0; q.odx = (const float*)h->ex[11].p + b0;
+        q.ody = (const float*)h->ex[12].p + b0;
+        const unsigned grid = (unsigned)((n + 127) / 128);
+        if (h->elem == 8)
+            k_tick_prepare<double><<<grid, 128, 0, st>>>(q, (double*)h->mA.p + b0, (double*)h->mB.p + b0, (double*)h->mC.p + b0,
+                                                         (double*)h->mQ.p + b0, (double*)h->mR.p + b0, (double*)h->mlo.p + b0,
+                                                         (double*)h->mhi.p + b0, (double*)h->x0.p + b0, (double*)h->target_const.p + b0,
+                                                         tgt_dbg + b0);
+        else
+            k_tick_prepare<float><<<grid, 128, 0, st>>>(q, (float*)h->mA.p + b0, (float*)h->mB.p + b0, (float*)h->mC.p + b0,
+                                                        (float*)h->mQ.p + b0, (float*)h->mR.p + b0, (float*)h->mlo.p + b0,
+                                                        (float*)h->mhi.p + b0, (float*)h->x0.p + b0, (float*)h->target_const.p + b0,
+                                                        tgt_dbg + b0);
+        BMPC_CUDA(cudaGetLastError());
         h->launches++;
-        BMPC_CUDA(cudaMemcpyAsync(target, h->stage.p, c * 2 * 8, cudaMemcpyDeviceToHost, st));
+        // ---- fresh controllers: constructor recursion (mpc.h:114-123), then one cold operator() each
+        const size_t off = (size_t)b0 * es;
+        GenericCtor g{n, h->cap, (char*)h->mA.p + off, (char*)h->mB.p + off, (char*)h->mQ.p + off, (char*)h->mR.p + off,
+                      (char*)h->mlambda.p + off, (char*)h->mqdiag.p + off};
+        BMPC_CUDA(h->ops->ctor(h->precision, h->mode, g, st));
+        h->launches++;
+        if ((rc = solve_range_async(h, b0, n, 0))) return rc;
+        // ---- CarCommand fields
+        if (h->elem == 8)
+            k_tick_finish<double><<<grid, 128, 0, st>>>(n, h->cap, (const double*)h->u0.p + b0, (const float*)h->ex[9].p + b0,
+                                                        (const float*)h->ex[10].p + b0, (const float*)h->ex[13].p + b0, d_sf + b0,
+                                                        d_sr + b0, d_ts + b0, d_td + b0, d_state + b0);
+        else
+            k_tick_finish<float><<<grid, 128, 0, st>>>(n, h->cap, (const float*)h->u0.p + b0, (const float*)h->ex[9].p + b0,
+                                                       (const float*)h->ex[10].p + b0, (const float*)h->ex[13].p + b0, d_sf + b0,
+                                                       d_sr + b0, d_ts + b0, d_td + b0, d_state + b0);
+        BMPC_CUDA(cudaGetLastError());
+        h->launches++;
+        const size_t m = (size_t)n;
+        BMPC_CUDA(cudaMemcpyAsync(steering_front + b0, d_sf + b0, m * 8, cudaMemcpyDeviceToHost, st));
+        BMPC_CUDA(cudaMemcpyAsync(steering_rear + b0, d_sr + b0, m * 8, cudaMemcpyDeviceToHost, st));
+        BMPC_CUDA(cudaMemcpyAsync(target_speed + b0, d_ts + b0, m * 4, cudaMemcpyDeviceToHost, st));
+        BMPC_CUDA(cudaMemcpyAsync(target_distance + b0, d_td + b0, m * 4, cudaMemcpyDeviceToHost, st));
+        BMPC_CUDA(cudaMemcpyAsync(state + b0, d_state + b0, m, cudaMemcpyDeviceToHost, st));
+        if (idx) BMPC_CUDA(cudaMemcpyAsync(idx + b0, (int32_t*)h->ex[7].p + b0, m * 4, cudaMemcpyDeviceToHost, st));
+        if (flag) BMPC_CUDA(cudaMemcpyAsync(flag + b0, (uint8_t*)h->ex[8].p + b0, m, cudaMemcpyDeviceToHost, st));
+        if (iters) BMPC_CUDA(cudaMemcpyAsync(iters + b0, (uint32_t*)h->iters.p + b0, m * 4, cudaMemcpyDeviceToHost, st));
+        if (target) {                                              // [count][2] = y_soll, phi_soll
+            BMPC_CUDA(soa_to_aos(tgt_dbg + b0, (double*)h->stage.p + 2 * b0, n, 2, h->cap, 8, st));
+            h->launches++;
+            BMPC_CUDA(cudaMemcpyAsync(target + 2 * b0, (double*)h->stage.p + 2 * b0, m * 2 * 8, cudaMemcpyDeviceToHost, st));
+        }
     }
     BMPC_CUDA(cudaStreamSynchronize(st));
     return BMPC_OK;

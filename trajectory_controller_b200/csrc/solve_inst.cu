@@ -37,10 +37,12 @@ void fill_params(SolveParams<T, S_, I_, N_>& p, const GenericSolve& g)
     p.eps = (T)g.eps; p.max_iter = g.max_iter;
     p.warm = g.warm; p.keep_controls = g.keep_controls; p.target_full = g.target_full; p.head = g.head;
     p.count = g.count; p.stride = g.stride;
-    p.x0 = (const T*)g.x0; p.controls = (T*)g.controls; p.vstate = (T*)g.vstate; p.target = (T*)g.target;
-    p.u0 = (T*)g.u0; p.iters = g.iters; p.status = g.status;
-    p.mA = (const T*)g.mA; p.mB = (const T*)g.mB; p.mC = (const T*)g.mC; p.mQ = (const T*)g.mQ; p.mR = (const T*)g.mR;
-    p.mlo = (const T*)g.mlo; p.mhi = (const T*)g.mhi; p.mlambda = (const T*)g.mlambda; p.mqdiag = (const T*)g.mqdiag;
+    // every per-instance array is [element][stride]: a launch on instances [first, first + count) shifts the bases
+    const long long f = g.first;
+    p.x0 = (const T*)g.x0 + f; p.controls = (T*)g.controls + f; p.vstate = (T*)g.vstate + f; p.target = (T*)g.target + f;
+    p.u0 = (T*)g.u0 + f; p.iters = g.iters + f; p.status = g.status + f;
+    p.mA = (const T*)g.mA + f; p.mB = (const T*)g.mB + f; p.mC = (const T*)g.mC + f; p.mQ = (const T*)g.mQ + f; p.mR = (const T*)g.mR + f;
+    p.mlo = (const T*)g.mlo + f; p.mhi = (const T*)g.mhi + f; p.mlambda = (const T*)g.mlambda + f; p.mqdiag = (const T*)g.mqdiag + f;
     p.queue = g.queue;
     p.split = g.split; p.pg_list = g.pg_list; p.pg_mask = g.pg_mask; p.pg_slice = g.pg_slice;
     p.park = (T*)g.park; p.park_iter = g.park_iter; p.pg_reuse = g.pg_reuse; p.sym = g.sym;
