@@ -1,10 +1,11 @@
-timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -4 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu --no-fast > gpurun_out/bench_a.json 2> gpurun_out/bench_a.err; echo "bench rc=$?"
-python - <<'PY'
-import json
-d=json.load(open('gpurun_out/bench_a.json')); r=d['roofline']
-print('value %.4e e2e %.4e ms %.3f stageA %.3f stageB %.3f lat %s'%(d['value'],d['e2e']['value'],d['ms_per_step'],r['whole_solve']['stage_a_ms'],r['whole_solve']['stage_b_ms'],d['latency_us_batch1']['p50']))
+for lib in "" roll; do
+  L=$PWD/trajectory_controller_b200/libbmpc.so; [ -n "$lib" ] && L=$PWD/trajectory_controller_b200/libbmpc_$lib.so
+  echo "== lib ${lib:-main}"
+  BMPC_LIB=$L timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_closed_loop.py -m gpu -x -q -k "bike_cold or split_solve or sweep_slice or closed_loop_matches or tolerance or config2" 2>&1 | tail -2
+  BMPC_LIB=$L timeout 600 python scripts/bench_multi.py sweep --reps 2 > gpurun_out/sweep_${lib:-main}.json 2> gpurun_out/sweep.err || tail -5 gpurun_out/sweep.err
+  python - ${lib:-main} <<'PY'
+import json,sys
+d=json.load(open('gpurun_out/sweep_%s.json'%sys.argv[1]))['results']
+print('sweep',sys.argv[1],{k:(round(v['solves_per_s']),round(v['kernel_ms_slowest_rank'],2),v['u0_checksum']) for k,v in d.items()})
 PY
-timeout 600 python scripts/bench_multi.py closed --ticks 105 > gpurun_out/closed_a.json 2>/dev/null; python -c "
-import json; d=json.load(open('gpurun_out/closed_a.json')); print('closed ms/tick', d['ms_per_tick'], d['solves_per_s'])"
+done

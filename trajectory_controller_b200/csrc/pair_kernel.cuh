@@ -40,6 +40,11 @@
 #ifndef BMPC_PAIR_CAP_WARPS
 #define BMPC_PAIR_CAP_WARPS 8
 #endif
+// Horizons from this length on run the pass as a ROLLED loop (two trips per iteration) with u / MM in shared memory:
+// the fully unrolled pass of a long horizon no longer fits the instruction cache (profiles/r2_experiments.md).
+#ifndef BMPC_PAIR_ROLL_MIN
+#define BMPC_PAIR_ROLL_MIN 1000
+#endif
 
 namespace bmpc {
 
@@ -49,13 +54,16 @@ struct PairLayout {
     static constexpr int NH = N / 2;                       // control entries per lane
     static constexpr int WORDS = int(sizeof(T) / 4);
     // u (NH entries) always lives in registers; MM too while both stay within 128 32-bit registers
-    static constexpr bool MMREG = (2 * NH * WORDS <= 128);
+    static constexpr bool ROLLED = (N >= BMPC_PAIR_ROLL_MIN);
+    static constexpr bool MMREG = !ROLLED && (2 * NH * WORDS <= 128);
+    static constexpr int UNR = ROLLED ? 2 : N + 2;         // horizon loops: full unroll keeps u[] / MM[] in registers
     // shared memory per lane, in elements: N pair slots (H: the Q*M stash of the forward sweep, slot s = horizon step s;
     // both lanes: (u_old, v_old) of the lane's own entry e in slot e once the backward sweep has consumed it), v, MM
     static constexpr int O_Q = 0;                          // slot s lives at pair index s + 1: one pad slot in front
     static constexpr int O_V = 2 * (N + 1);
     static constexpr int O_MM = O_V + NH;
-    static constexpr int ELEMS = O_MM + (MMREG ? 0 : NH);
+    static constexpr int O_U = O_MM + (MMREG ? 0 : NH);
+    static constexpr int ELEMS = O_U + (ROLLED ? NH : 0);
     static constexpr int WARP_BYTES = ELEMS * 32 * int(sizeof(T));
     static constexpr int FIT = kSmemMax / WARP_BYTES;
     static constexpr int WARPS = imax_c(1, imin_c(FIT, BMPC_PAIR_CAP_WARPS));
@@ -79,7 +87,7 @@ struct PairSolver {
     T b3, R, hi, inv_lambda, beta, eps;
     bool isH;
     unsigned a1, a2, a2own, a2lag;   // shared-window byte addresses: single elements / pair slots / slot + role (own entries) / slot + (L ? 1 : 0)
-    T u[NH];
+    T u[L::ROLLED ? 1 : NH];
     T mm[L::MMREG ? NH : 1];
     unsigned long long sat;          // bit j set <=> |u[j]| == hi (entry sits on a bound), own entries
 
@@ -89,6 +97,8 @@ struct PairSolver {
     __device__ __forceinline__ unsigned elem_addr(int e) const { return a1 + (unsigned)(e * 32 * ES); }
     __device__ __forceinline__ T getV(int j) const { return IO::ld1(elem_addr(L::O_V + j)); }
     __device__ __forceinline__ void setV(int j, T v) { IO::st1(elem_addr(L::O_V + j), v); }
+    __device__ __forceinline__ T getU(int j) const { if constexpr (L::ROLLED) return IO::ld1(elem_addr(L::O_U + j)); else return u[j]; }
+    __device__ __forceinline__ void setU(int j, T v) { if constexpr (L::ROLLED) IO::st1(elem_addr(L::O_U + j), v); else u[j] = v; }
     __device__ __forceinline__ T getMM(int j) const { if constexpr (L::MMREG) return mm[j]; else return IO::ld1(elem_addr(L::O_MM + j)); }
     __device__ __forceinline__ void setMM(int j, T v) { if constexpr (L::MMREG) mm[j] = v; else IO::st1(elem_addr(L::O_MM + j), v); }
 
@@ -121,7 +131,7 @@ struct PairSolver {
     {
         sat = 0;
 #pragma unroll
-        for (int j = 0; j < NH; ++j) sat |= (unsigned long long)(!PS::inside(u[j], hi)) << j;
+        for (int j = 0; j < NH; ++j) sat |= (unsigned long long)(!PS::inside(getU(j), hi)) << j;
     }
 
     // One projected-gradient iteration of the pair's instance.  Returns true when the reference would NOT break at
@@ -137,18 +147,21 @@ struct PairSolver {
     __device__ __forceinline__ bool pass()
     {
         // ---------------- forward sweep: M[i] = A*M[i-1] + B*u[i] (mpc.h:275-277), Q-scaling and stash (mpc.h:279)
-        T r_old = xchg(isH ? u[0] : T(0));                            // L: control entry 1;  H: "m2 of step -1" = 0
+        const T u_first = getU(0);
+        T r_old = xchg(isH ? u_first : T(0));                         // L: control entry 1;  H: "m2 of step -1" = 0
         T pcur = T(0);
-        T qcur = A_::mul(c3, isH ? T(0) : u[0]);                      // trip 0, L: M[0] = B*u[0] (m3 = b3*u0);  H: zeros
+        T qcur = A_::mul(c3, isH ? T(0) : u_first);                      // trip 0, L: M[0] = B*u[0] (m3 = b3*u0);  H: zeros
         T r_new = xchg(pcur);                                         // H: m2 of step 0;  (L: unused)
         T wp = T(0), wq = T(0);
-#pragma unroll
+        T ucur = T(0);                                                // own control entry (k+1)/2, fetched at the start of odd trip k
+#pragma unroll(L::UNR)
         for (int k = 1; k <= N; ++k) {
+            if ((k & 1) && k <= N - 3) ucur = getU((k + 1) / 2);      // used by the exchange of this trip (H) and as Y of the next (L)
             // Y: L reads control entry k (own if k is even, received if odd); H reads L's m2 of step k-2
             T Y;
             if (k == N) Y = isH ? r_old : T(0);                       // L has no step N: its numbers of this trip are unused
             else if (k & 1) Y = r_old;
-            else Y = isH ? r_old : u[k / 2];
+            else Y = isH ? r_old : ucur;
             const T pn = A_::madd(pcur, cP, qcur);
             const T t12 = A_::madd(A_::mul(c1, pcur), c2, qcur);
             T qn;
@@ -162,7 +175,7 @@ struct PairSolver {
             r_old = r_new;
             if (k <= N - 2) {
                 // end of trip k: H sends the control entry of L's step k+2 (needed when k is odd), L sends m2 of step k
-                if (k & 1) r_new = xchg(isH ? u[(k + 1) / 2] : pcur);
+                if (k & 1) r_new = xchg(isH ? ucur : pcur);
                 else r_new = xchg(pcur);
             }
         }
@@ -181,20 +194,24 @@ struct PairSolver {
         IO::ld2(lag_addr(N - 2), s0, s1);                             // stash of trip 1
         T vo = getV(NH - 1);                                          // v of the first update (trip 3)
         T mmv = getMM(NH - 1);
-        T pend_u = T(0), pend_vold = T(0), pend_vn = T(0);            // the previous update's stores
-#pragma unroll
+        T uo_ = getU(NH - 1);
+        T pend_u = T(0), pend_vold = T(0), pend_vn = T(0), pend_un = T(0);   // the previous update's stores
+#pragma unroll(L::UNR)
         for (int k = 1; k <= N + 1; ++k) {
             const T X = r_old;                                        // L: w1 of step N-k+1;  H: w3 of step N-k+2
             T s0f = T(0), s1f = T(0);
             if (k + 1 <= N) IO::ld2(lag_addr(N - 2 - k), s0f, s1f);   // stash of trip k+1
             const bool upd = (k & 1) && k >= 3;
             const int j = (N + 1 - k) / 2;                            // L: entry N+1-k = 2j, H: entry N+2-k = 2j+1
-            T vof = T(0), mmf = T(0);
-            if (upd && j >= 1) { vof = getV(j - 1); mmf = getMM(j - 1); }                             // for the update two trips on
-            if (upd && j + 1 <= NH - 1) { IO::st2(own_addr(j + 1), pend_u, pend_vold); setV(j + 1, pend_vn); }   // ... and of two trips ago
+            T vof = T(0), mmf = T(0), uf = T(0);
+            if (upd && j >= 1) { vof = getV(j - 1); mmf = getMM(j - 1); uf = getU(j - 1); }           // for the update two trips on
+            if (upd && j + 1 <= NH - 1) {                                                             // ... and of two trips ago
+                IO::st2(own_addr(j + 1), pend_u, pend_vold); setV(j + 1, pend_vn);
+                if constexpr (L::ROLLED) setU(j + 1, pend_un);
+            }
             if (upd) {
                 const T w3 = isH ? X : qcur;
-                const T uij = u[j];
+                const T uij = uo_;
                 const T dfv = A_::add(A_::add(mmv, A_::mul(b3, w3)), A_::mul(R, uij));               // mpc.h:283
                 const bool big = absval(dfv) >= eps;
                 const bool blocked = ((sat >> j) & 1ull) != 0 && PS::sign_differs(dfv, uij);           // mpc.h:296-299
@@ -203,10 +220,11 @@ struct PairSolver {
                 const T vn = PS::clamp_sym(t1, hi, PS::inside(t1, hi));
                 const T t2 = A_::madd(vn, beta, A_::sub(vn, vo));                                      // mpc.h:344
                 const bool in2 = PS::inside(t2, hi);
-                u[j] = PS::clamp_sym(t2, hi, in2);
+                const T un = PS::clamp_sym(t2, hi, in2);
+                if constexpr (!L::ROLLED) setU(j, un);                 // registers; the rolled form stores it with the next update
                 nsat |= (unsigned long long)(!in2) << j;
-                pend_u = uij; pend_vold = vo; pend_vn = vn;            // the slot of this entry's step has been consumed: stored next update
-                vo = vof; mmv = mmf;
+                pend_u = uij; pend_vold = vo; pend_vn = vn; pend_un = un;   // the slot of this entry's step has been consumed: stored next update
+                vo = vof; mmv = mmf; uo_ = uf;
             }
             if (k <= N) {
                 // H: step N-1-k from slot N-1-k;  L: step N-k, whose slot holds the zeros the forward sweep stored
@@ -223,6 +241,7 @@ struct PairSolver {
             if (k <= N - 1) r_new = xchg(qcur);                       // end of trip k: H's w1 of step N-1-k, L's w3 of step N-k
         }
         IO::st2(own_addr(0), pend_u, pend_vold); setV(0, pend_vn);    // the last update's stores
+        if constexpr (L::ROLLED) setU(0, pend_un);
         sat = nsat;
         return __shfl_xor_sync(0xffffffffu, (int)notconv, 1) != 0 || notconv;
     }
@@ -268,7 +287,7 @@ pair_kernel(const __grid_constant__ SolveParams<T, 4, 1, N> p)
     if constexpr (!PIM)
         sv.set_model(role != 0, p.A[1], p.A[6], p.A[11], p.A[14], p.A[15], p.B[3], p.Q[0], p.Q[1], p.R[0], p.hi[0], p.lambda, p.eps);
 #pragma unroll
-    for (int j = 0; j < NH; ++j) { sv.u[j] = T(0); sv.setMM(j, T(0)); }
+    for (int j = 0; j < NH; ++j) { sv.setU(j, T(0)); sv.setMM(j, T(0)); }
 
     bool need = true, active = false;
     uint32_t iter = 0, inst = 0;
@@ -296,7 +315,7 @@ pair_kernel(const __grid_constant__ SolveParams<T, 4, 1, N> p)
                     const long long step2 = 2 * rstride;
 #pragma unroll
                     for (int j = 0; j < NH; ++j) {
-                        sv.u[j] = __ldcg(su);
+                        sv.setU(j, __ldcg(su));
                         sv.setV(j, __ldcg(sv_));
                         sv.setMM(j, __ldcg(sm_));
                         su += step2; sv_ += step2; sm_ += step2;
@@ -337,7 +356,7 @@ pair_kernel(const __grid_constant__ SolveParams<T, 4, 1, N> p)
 #pragma unroll
             for (int j = 0; j < NH; ++j) {
                 T uo, vo;
-                if (hit_max) { uo = sv.u[j]; vo = sv.getV(j); }
+                if (hit_max) { uo = sv.getU(j); vo = sv.getV(j); }
                 else SV::IO::ld2(sv.own_addr(j), uo, vo);              // converged: the iterate the test was taken on
                 if (j == 0 && role == 0) p.u0[inst] = uo;                                             // mpc.h:239
                 if (wc) *dc = uo;
