@@ -12,3 +12,4 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/b
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:solve_kernel|pg_kernel|pair_kernel' -s 9 -c 3 -o gpurun_out/solve_full -f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1
 ls -la gpurun_out
+timeout 600 python scripts/sanitize.py > gpurun_out/sanitize_plain.log 2>&1; tail -12 gpurun_out/sanitize_plain.log
