@@ -1,4 +1,1 @@
-timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -3 gpurun_out/pytest_gpu.log
-SAN_B=700 timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 9 python scripts/sanitize.py > gpurun_out/san_memcheck.log 2>&1; echo "memcheck rc=$?"; tail -4 gpurun_out/san_memcheck.log
-SAN_B=300 timeout 1500 compute-sanitizer --tool racecheck --error-exitcode 9 python scripts/sanitize.py > gpurun_out/san_racecheck.log 2>&1; echo "racecheck rc=$?"; tail -4 gpurun_out/san_racecheck.log
+timeout 600 python scripts/stress_stages.py > gpurun_out/stress.log 2>&1; echo "stress rc=$?"; grep -c " ok " gpurun_out/stress.log; grep -v " ok " gpurun_out/stress.log | tail -5

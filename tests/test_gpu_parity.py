@@ -520,6 +520,29 @@ def test_config3_one_million_instances_properties(oracle):
         assert same_values(u1, -u0) and np.array_equal(it1, it)
 
 
+@pytest.mark.parametrize("eps,max_iter", [(0.01, 10000), (0.01, 60), (0.001, 3000)])
+def test_stage_thresholds_are_invisible(eps, max_iter):
+    """Batch sizes around every scheduling threshold of the staged solve (stage C direct up to 9,472 instances; above it
+    stage B with the hand-over of its last 9,472; time slices from 37,889; small max_iterations end instances inside every
+    stage): bit-equal to stages A + B alone (bmpc_set_split 2), cold and over a warm sequence."""
+    bike, cap = W.bicycle4_model(), 80000
+    x0 = W.random_offsets_x0(cap, 7)
+    with BatchedMPC(4, 1, 30, cap) as a, BatchedMPC(4, 1, 30, cap) as b:
+        a.set_model(bike); b.set_model(bike); b.set_split(2)
+        a.set_options(eps, max_iter); b.set_options(eps, max_iter)
+        for n in (1, 33, 9471, 9473, 18945, 37889, 75777):
+            ua, ia, sa = a.solve(x0[:n]); ub, ib, sb = b.solve(x0[:n])
+            assert np.array_equal(ua.view(np.uint64), ub.view(np.uint64)) and np.array_equal(ia, ib) and np.array_equal(sa, sb), n
+        n = 40000
+        a.reset(); b.reset()
+        x = x0[:n].copy()
+        for tick in range(3):
+            ua, ia, _ = a.solve(x, warm=True); ub, ib, _ = b.solve(x, warm=True)
+            assert np.array_equal(ua.view(np.uint64), ub.view(np.uint64)) and np.array_equal(ia, ib), tick
+            x = x * 0.8; x[:, 2] += 0.1 * ua[:, 0]
+        assert np.array_equal(a.get_controls(n).view(np.uint64), b.get_controls(n).view(np.uint64))
+
+
 def test_time_slicing_is_invisible():
     """Stage B parks and resumes instances every 128 iterations when a batch gives each lane 1-4 instances
     (bmpc_solve.cu).  65,536 and 100,000 instances with time slicing (split = 1), without (2) and on the one-kernel
