@@ -1,1 +1,1 @@
-timeout 600 python scripts/stress_stages.py > gpurun_out/stress.log 2>&1; echo "stress rc=$?"; grep -c " ok " gpurun_out/stress.log; grep -v " ok " gpurun_out/stress.log | tail -5
+timeout 600 python scripts/bench_group.py > gpurun_out/r2_group.json 2> gpurun_out/group.err || tail -5 gpurun_out/group.err; cat gpurun_out/r2_group.json | cut -c1-900
