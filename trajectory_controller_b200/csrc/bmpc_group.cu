@@ -260,13 +260,16 @@ int bmpc_group_solve(bmpc_group_t* g, int64_t count, const double* x0, double* u
     if (!g || !x0 || !u0) return fail(BMPC_E_INVALID, "bmpc_group_solve: null argument");
     if (count < 1 || count > g->cap) return fail(BMPC_E_INVALID, "bmpc_group_solve: count out of capacity");
     const int S = g->S, I = g->I;
-    return g->run([&](int k) -> int {
-        const long long n = g->local_count(k, count);
-        if (n == 0) return BMPC_OK;
-        if (g->assignment == BMPC_GROUP_CONTIGUOUS) {
+    if (g->assignment == BMPC_GROUP_CONTIGUOUS)
+        return g->run([&](int k) -> int {
+            const long long n = g->local_count(k, count);
+            if (n == 0) return BMPC_OK;
             const long long f = g->first_global(k);
             return bmpc_solve(g->h[k], n, x0 + f * S, u0 + f * I, iters ? iters + f : nullptr, status ? status + f : nullptr, flags);
-        }
+        });
+    const int rc1 = g->run([&](int k) -> int {
+        const long long n = g->local_count(k, count);
+        if (n == 0) return BMPC_OK;
         cudaSetDevice(g->dev[k]);
         int rc;
         if ((rc = g->pin_in[k].reserve((size_t)n * S * 8))) return rc;
@@ -278,12 +281,25 @@ int bmpc_group_solve(bmpc_group_t* g, int64_t count, const double* x0, double* u
         uint32_t* pi = (uint32_t*)((char*)g->pin_out[k].p + ob);
         uint8_t* ps = (uint8_t*)g->pin_out[k].p + ob + ib;
         pack(g, k, n, S, x0, px);
-        if ((rc = bmpc_solve(g->h[k], n, px, pu, iters ? pi : nullptr, status ? ps : nullptr, flags))) return rc;
-        for (long long j = 0; j < n; ++j) {
-            const long long i = g->global_of(k, j);
+        return bmpc_solve(g->h[k], n, px, pu, iters ? pi : nullptr, status ? ps : nullptr, flags);
+    });
+    if (rc1) return rc1;
+    // The gather into the caller's arrays is split by OUTPUT range, not by member: worker k writes the contiguous block
+    // [k*count/ndev, (k+1)*count/ndev) from every member's staging (neighbouring instances belong to different members,
+    // and eight threads writing into the same cache lines cost 4 ms per million instances).
+    const int nd = g->ndev;
+    std::vector<long long> held(nd);
+    for (int m = 0; m < nd; ++m) held[m] = g->local_count(m, count);
+    return g->run([&](int k) -> int {
+        const long long lo = count * k / nd, hi = count * (k + 1) / nd;
+        for (long long i = lo; i < hi; ++i) {
+            const int m = (int)(i % nd);
+            const long long j = i / nd, nm = held[m];
+            const char* base = (const char*)g->pin_out[m].p;
+            const double* pu = (const double*)base;
             for (int c = 0; c < I; ++c) u0[i * I + c] = pu[j * I + c];
-            if (iters) iters[i] = pi[j];
-            if (status) status[i] = ps[j];
+            if (iters) iters[i] = ((const uint32_t*)(base + (size_t)nm * I * 8))[j];
+            if (status) status[i] = ((const uint8_t*)(base + (size_t)nm * I * 8 + (size_t)nm * 4))[j];
         }
         return BMPC_OK;
     });
