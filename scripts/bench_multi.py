@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """BASELINE.json configs[2], [3], [4] at 1/2/4/8 GPUs: a FIXED global problem is
 sharded by instance over the ranks (strong scaling), one process per GPU, and the job's only collective — the final
-result gather (NCCL all_gather of u0 / iteration counts / status out of the engines' result buffers in HBM, then a D2H
-of the gathered arrays on every rank) — is INSIDE the timed region.  One JSON line per run (rank 0).
+result gather (ONE NCCL all_gather of every rank's result block u0 | iteration counts | status out of HBM, then a D2H of
+the gathered job into pinned host memory on rank 0) — is INSIDE the timed region.  One JSON line per run (rank 0).
 
     python scripts/bench_multi.py tolerance|sweep|closed                                     # one GPU
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
@@ -14,8 +14,8 @@ of the gathered arrays on every rank) — is INSIDE the timed region.  One JSON 
              round-robin instance assignment (the combos are blocked and differ 100x in iteration counts)
   closed     config 5: 262,144 vehicles x 500 ticks on the device, FP64 EXACT; gather of the final poses
 
-Timing: the region runs from pinned HOST inputs (H2D of the rank's shard inside) to the gathered results in pinned
-host memory on every rank; barrier + cudaDeviceSynchronize on both sides, wall clock, MAX over ranks; the kernels'
+Timing: the region runs from pinned HOST inputs (H2D of the rank's shard inside) to the gathered results in HBM on every
+rank and in pinned host memory on rank 0; barrier + cudaDeviceSynchronize on both sides, wall clock, MAX over ranks; the kernels'
 share is reported from CUDA events.  Clocks and throttle reasons are sampled during the timed region."""
 from __future__ import annotations
 
@@ -81,37 +81,42 @@ class Job:
 
 
 class Gather:
-    """all_gather of the engine's device-resident results (u0 [I][cap], iters, status) + D2H on every rank.
-    Rank r holds the global instances r, r + world, ... (round robin): row-major [cap][world] of the gathered
-    [world][cap] array is global instance order."""
+    """The job's only collective: ONE all_gather of every rank's result block (u0 [I][cap] | iters | status live in one
+    device allocation, bmpc_device_results_block) — afterwards every rank holds the whole job's results in HBM — plus one
+    D2H of the gathered blocks into pinned host memory on rank 0.  Rank r holds the global instances r, r + world, ...
+    (round robin): row-major [cap][world] of the gathered [world][cap] arrays is global instance order."""
 
     def __init__(self, job: Job, eng: BatchedMPC, count: int):
         t = job.torch
         self.job, self.count, self.world = job, count, job.world
-        self.du0, self.dit, self.dst = (t.as_tensor(v, device=job.dev) for v in eng.device_results())
-        cap, I = eng.capacity, eng.I
-        self.g = [t.empty((job.world,) + tuple(x.shape), dtype=x.dtype, device=job.dev) for x in (self.du0, self.dit, self.dst)]
-        self.h = [t.empty(x.shape, dtype=x.dtype).pin_memory() for x in self.g]
-        self.bytes_out = sum(x.numel() * x.element_size() for x in self.g)
-        self.cap, self.I = cap, I
+        view, self.off_it, self.off_st = eng.device_results_block()
+        self.dblk = t.as_tensor(view, device=job.dev)
+        n = self.dblk.numel()
+        self.g = t.empty((job.world, n), dtype=t.uint8, device=job.dev)
+        self.h = t.empty((job.world, n), dtype=t.uint8).pin_memory()
+        self.bytes_out = job.world * n
+        self.cap, self.I = eng.capacity, eng.I
+        self.ftype = np.float64 if eng.precision == FP64 else np.float32
 
     def __call__(self):
-        d = self.job.dist
-        for g, src in zip(self.g, (self.du0, self.dit, self.dst)):
-            if self.world > 1:
-                d.all_gather_into_tensor(g.view(-1), src.reshape(-1))
-            else:
-                g[0].copy_(src)
-        for h, g in zip(self.h, self.g):
-            h.copy_(g, non_blocking=True)
+        if self.world > 1:
+            self.job.dist.all_gather_into_tensor(self.g.view(-1), self.dblk)
+        else:
+            self.g[0].copy_(self.dblk)
+        if self.job.rank == 0:
+            self.h.copy_(self.g, non_blocking=True)
 
     def results(self):
-        """(u0[count][I] float64, iters[count], status[count]) in global instance order."""
+        """(u0[count][I] float64, iters[count], status[count]) in global instance order (outside the timed region)."""
         self.job.torch.cuda.synchronize()
-        u0 = self.h[0].numpy().astype(np.float64)                    # [world][I][cap]
-        u0 = np.ascontiguousarray(u0.transpose(2, 0, 1)).reshape(self.cap * self.world, self.I)[: self.count]
-        it = np.ascontiguousarray(self.h[1].numpy().T).reshape(-1)[: self.count].view(np.uint32).astype(np.int64)
-        st = np.ascontiguousarray(self.h[2].numpy().T).reshape(-1)[: self.count]
+        blk = self.h.numpy() if self.job.rank == 0 else self.g.cpu().numpy()
+        cap, I, w = self.cap, self.I, self.world
+        es = np.dtype(self.ftype).itemsize
+        u0 = blk[:, : I * cap * es].copy().view(self.ftype).reshape(w, I, cap).astype(np.float64)
+        u0 = np.ascontiguousarray(u0.transpose(2, 0, 1)).reshape(cap * w, I)[: self.count]
+        it = blk[:, self.off_it: self.off_it + 4 * cap].copy().view(np.uint32).reshape(w, cap)
+        it = np.ascontiguousarray(it.T).reshape(-1)[: self.count].astype(np.int64)
+        st = np.ascontiguousarray(blk[:, self.off_st: self.off_st + cap].T).reshape(-1)[: self.count]
         return u0, it, st
 
 

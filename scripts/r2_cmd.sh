@@ -1,3 +1,6 @@
-./tests/cpp/build/test_group 2>&1 | tail -3
-timeout 600 python -m pytest tests/test_group.py -m gpu -x -q 2>&1 | tail -2
-timeout 600 python scripts/bench_group.py > gpurun_out/r2_group.json 2> gpurun_out/group.err || tail -5 gpurun_out/group.err; cat gpurun_out/r2_group.json | cut -c1-900
+timeout 600 python scripts/bench_multi.py tolerance --batch 262144 --reps 1 > gpurun_out/tol_check.json 2> gpurun_out/tol.err || tail -5 gpurun_out/tol.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/tol_check.json'))['results']
+print({k:(round(v['solves_per_s']),v['max_abs_du'],v['iters_equal_frac'],v['iters_mean']) for k,v in d.items()})
+PY
