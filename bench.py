@@ -73,36 +73,62 @@ def config_dict(args, world):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi SM clock + throttle reasons, sampled while the timed region runs."""
+    """SM clock + throttle reasons, sampled while the timed region runs: NVML in-process (pynvml) when it loads — a
+    sample costs microseconds, nothing is forked — else one `nvidia-smi` query per sample."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active"
+    NAMES = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+             0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+             0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
 
-    def __init__(self, index: int, period: float = 0.05):
+    def __init__(self, index: int, period: float = 0.02):
         super().__init__(daemon=True)
         self.index, self.stop_flag, self.samples, self.reasons, self.maxmhz = index, threading.Event(), [], set(), None
-        self.period = period
+        self.period, self.source = period, None
+
+    def _note(self, mhz: float, max_mhz: float, bits: int):
+        self.samples.append(float(mhz)); self.maxmhz = float(max_mhz)
+        for b, n in self.NAMES.items():
+            if bits & b and n != "gpu_idle":
+                self.reasons.add(n)
+
+    def _run_nvml(self) -> bool:
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            dev = nv.nvmlDeviceGetHandleByIndex(self.index)
+            reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            max_mhz = nv.nvmlDeviceGetMaxClockInfo(dev, nv.NVML_CLOCK_SM)
+            nv.nvmlDeviceGetClockInfo(dev, nv.NVML_CLOCK_SM); reasons(dev)          # fail here, not mid-run
+        except Exception:
+            return False
+        self.source = "nvml"
+        while not self.stop_flag.is_set():
+            try:
+                self._note(nv.nvmlDeviceGetClockInfo(dev, nv.NVML_CLOCK_SM), max_mhz, int(reasons(dev)))
+            except Exception:
+                pass
+            self.stop_flag.wait(self.period)
+        return True
 
     def run(self):
-        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
-                 0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
-                 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        if self._run_nvml():
+            return
+        self.source = "nvidia-smi"
         while not self.stop_flag.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
                 f = [x.strip() for x in out.strip().split(",")]
-                self.samples.append(float(f[0])); self.maxmhz = float(f[1])
-                bits = int(f[2], 16) if f[2].lower().startswith("0x") else 0
-                for b, n in names.items():
-                    if bits & b and n != "gpu_idle":
-                        self.reasons.add(n)
+                self._note(float(f[0]), float(f[1]), int(f[2], 16) if f[2].lower().startswith("0x") else 0)
             except Exception:
                 pass
-            self.stop_flag.wait(self.period)
+            self.stop_flag.wait(max(self.period, 0.05))
 
     def result(self):
         self.stop_flag.set(); self.join(timeout=6)
         med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.maxmhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        return {"sm_mhz": med, "sm_max_mhz": self.maxmhz, "reasons": sorted(self.reasons), "samples": len(self.samples),
+                "source": self.source}
 
 
 # ------------------------------------------------------------------------------------------------- CPU legs
@@ -281,9 +307,8 @@ def run_ours(args):
             eng.solve_resident_async(B)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
         barrier()
-        # one sampler per job: every sample forks nvidia-smi, and 8 ranks x 20 forks/s would starve the host threads
-        # that drive the end-to-end loop
-        sampler = ClockSampler(local, period=0.05 if world == 1 else 0.25)
+        # one sampler per job (rank 0), NVML in-process: nothing is forked beside the host threads that drive the loop
+        sampler = ClockSampler(local, period=0.02)
         if rank == 0:
             sampler.start()
         l0 = eng.launch_count()

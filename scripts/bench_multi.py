@@ -68,10 +68,10 @@ class Job:
         return t
 
     def sampler(self):
-        """Clock / throttle sampler of the job: rank 0 only (every sample forks nvidia-smi; eight samplers starve the host)."""
+        """Clock / throttle sampler of the job: rank 0 only (one sampler per job is enough; NVML in-process, bench.ClockSampler)."""
         if self.rank != 0:
             return None
-        sm = ClockSampler(self.local, period=0.05 if self.world == 1 else 0.25)
+        sm = ClockSampler(self.local, period=0.05)
         sm.start()
         return sm
 
