@@ -186,6 +186,24 @@ int bmpc_extract_horizon(bmpc_t* h, int64_t count, int P, const int32_t* npoints
                          int64_t stride_point, const float* d0, const float* step, int steps, int32_t* idx,
                          uint8_t* flag, float* out_px, float* out_py, float* out_dx, float* out_dy, float* out_vel);
 
+/* bmpc_extract_points without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code beside a CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  No handle: `device` is the CUDA device index, `cuda_stream` a cudaStream_t (NULL: default stream).
+ * Arguments, results and bit-exactness as for bmpc_extract_points (host arrays in, host arrays out); the device staging
+ * lives in ONE file-scope device array of BMPC_STATIC_EXTRACT_BYTES inside the library (every GPU that loads libbmpc.so
+ * holds it until the process exits), and the call makes no cudaMalloc / cudaFree / allocating library call.
+ * A problem whose staging — five polyline arrays of (count-1)*stride_instance + (P-1)*stride_point + 1 floats, dist,
+ * npoints and seven outputs of `count` elements, each rounded up to 256 bytes — exceeds the array is rejected with
+ * BMPC_E_INVALID (bmpc_last_error() names the sizes): use bmpc_extract_points for it.
+ * All calls on a device share the array, which keeps the last call's contents (its output window is cleared at the
+ * start of every call).  Synchronous on return, and concurrent callers are serialised inside the library, so calls made
+ * through this entry point never overlap on the GPU; work that did overlap on the array would race. */
+#define BMPC_STATIC_EXTRACT_BYTES (4u << 20)
+int bmpc_extract_points_static(int device, void* cuda_stream, int64_t count, int P, const int32_t* npoints,
+                               const float* px, const float* py, const float* dx, const float* dy, const float* vel,
+                               int64_t stride_instance, int64_t stride_point, const float* dist, int32_t* idx,
+                               uint8_t* flag, float* out_px, float* out_py, float* out_dx, float* out_dy, float* out_vel);
+
 /* ---- closed loop on the device  (BASELINE.json configs[4]) ------------------------------------
  * Every tick, for every vehicle, without a host round trip:
  *   sample the world path into a vehicle-frame polyline of P float points (what the TRAJECTORY channel carries)

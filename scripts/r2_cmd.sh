@@ -1,6 +1,7 @@
-timeout 600 python scripts/bench_multi.py tolerance --batch 262144 --reps 1 > gpurun_out/tol_check.json 2> gpurun_out/tol.err || tail -5 gpurun_out/tol.err
-python - <<'PY'
-import json
-d=json.load(open('gpurun_out/tol_check.json'))['results']
-print({k:(round(v['solves_per_s']),v['max_abs_du'],v['iters_equal_frac'],v['iters_mean']) for k,v in d.items()})
-PY
+#!/bin/bash
+# scratch: the no-allocation entry point alone in a fresh process, then the whole round session
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > gpurun_out/pytest_no_alloc_alone.log 2>&1; echo "alone rc=$?" >> gpurun_out/pytest_no_alloc_alone.log
+tail -3 gpurun_out/pytest_no_alloc_alone.log
+bash scripts/gpu_round.sh
+tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench_exact64.json

@@ -67,6 +67,8 @@ SIGNATURES = {
     "bmpc_kernel_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 4),
     "bmpc_probe_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "bmpc_extract_points": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 + [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
+    "bmpc_extract_points_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int, _i32p] + [_fp] * 5 +
+                                   [C.c_int64, C.c_int64, _fp, _i32p, _u8p] + [_fp] * 5),
     "bmpc_fleet_tick_tobi": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, _fp, _dp, _fp, C.c_int, _i32p] + [_fp] * 5 +
                              [C.c_int64, C.c_int64, _dp, _dp, _fp, _fp, _u8p, _i32p, _u8p, _dp, _u32p]),
     "bmpc_set_lookup": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _fp, _fp]),
@@ -509,6 +511,33 @@ class BatchedMPC:
         _check(lib().bmpc_extract_points(self._h, B, P, _p(npts, _i32p), *[_p(a, _fp) for a in arrs], si, sp,
                                          _p(dist, _fp), _p(idx, _i32p), _p(flag, _u8p), *[_p(o, _fp) for o in outs]))
         return idx, flag, outs
+
+
+STATIC_EXTRACT_BYTES = 4 << 20          # BMPC_STATIC_EXTRACT_BYTES (include/bmpc.h)
+
+
+def extract_points_static(px, py, dx, dy, vel, dist, npoints=None, layout: str = "shared", device: int = 0, stream: int = 0):
+    """BatchedMPC.extract_points without a handle and without any allocation on the device (bmpc_extract_points_static:
+    the staging is a fixed array inside libbmpc.so, STATIC_EXTRACT_BYTES; larger problems raise).  Same arguments and
+    results; `stream` is a cudaStream_t as an integer (0: default stream)."""
+    arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (px, py, dx, dy, vel)]
+    dist = np.ascontiguousarray(dist, dtype=np.float32)
+    B = dist.shape[0]
+    if layout == "shared":
+        P, si, sp = arrs[0].shape[0], 0, 1
+    elif layout == "pb":
+        P, si, sp = arrs[0].shape[0], 1, B
+    elif layout == "bp":
+        P, si, sp = arrs[0].shape[1], arrs[0].shape[1], 1
+    else:
+        raise ValueError(layout)
+    npts = None if npoints is None else np.ascontiguousarray(npoints, dtype=np.int32)
+    idx = np.empty(B, dtype=np.int32); flag = np.empty(B, dtype=np.uint8)
+    outs = [np.empty(B, dtype=np.float32) for _ in range(5)]
+    _check(lib().bmpc_extract_points_static(int(device), C.c_void_p(stream or None), B, P, _p(npts, _i32p),
+                                            *[_p(a, _fp) for a in arrs], si, sp, _p(dist, _fp), _p(idx, _i32p),
+                                            _p(flag, _u8p), *[_p(o, _fp) for o in outs]))
+    return idx, flag, outs
 
 
 class ShardedMPC:
