@@ -71,6 +71,13 @@ def test_static_extract_on_a_caller_stream_and_without_a_handle(oracle):
         _same(extract_points_static(*arrs, dist, layout="bp", device=0, stream=st.cuda_stream), want, "stream")
 
 
+def test_static_extract_limit_matches_the_header():
+    import os, re
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "bmpc.h")).read()
+    m = re.search(r"#define\s+BMPC_STATIC_EXTRACT_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", hdr)
+    assert m and (int(m.group(1)) << int(m.group(2))) == E.STATIC_EXTRACT_BYTES
+
+
 def test_static_extract_rejects_what_does_not_fit():
     """The size and argument checks come before the first CUDA call: this part runs without a GPU."""
     z = np.zeros(8, dtype=np.float32)
