@@ -1,7 +1,5 @@
 #!/bin/bash
-# scratch: the no-allocation entry point alone in a fresh process, then the whole round session
+# scratch: per-call host latency of the facade's sequence + module cycle time
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > gpurun_out/pytest_no_alloc_alone.log 2>&1; echo "alone rc=$?" >> gpurun_out/pytest_no_alloc_alone.log
-tail -3 gpurun_out/pytest_no_alloc_alone.log
-bash scripts/gpu_round.sh
-tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench_exact64.json
+for i in 1 2; do timeout 120 scripts/probes/call_latency; done | tee gpurun_out/call_latency.jsonl
+timeout 120 tests/cpp/build/module_driver trajectory_controller_b200/cpp/build/libtrajectory_point_controller.so --time 2000 | tail -1 | tee gpurun_out/module_time.json
