@@ -152,7 +152,8 @@ int bmpc_set_stream(bmpc_t* h, void* cuda_stream);
  * the launch geometry of the solve kernel (for roofline bookkeeping). */
 int bmpc_last_kernel_ms(bmpc_t* h, float* ms);
 /* Two-stage solve: device time of stage A (set-up + coordinate phase) and stage B (projected-gradient kernel) of
- * the last solve; stage_b_ms = 0 when the solve ran as one kernel.  Launch geometry of the stage-B kernel. */
+ * the last solve; stage_b_ms = 0 when the solve ran as one kernel or was a small call (bmpc_solve of up to 16
+ * instances records no stage event).  Launch geometry of the stage-B kernel. */
 int bmpc_last_stage_ms(bmpc_t* h, float* stage_a_ms, float* stage_b_ms);
 int bmpc_pg_kernel_info(bmpc_t* h, int* grid, int* block, int* smem_bytes, int* regs);
 int64_t bmpc_launch_count(bmpc_t* h);

@@ -43,9 +43,10 @@ int main()
         const double c = now_us();
         t_solve_only.push_back(b - a); t_sync.push_back(c - b);
     }
+    float kms = 0; bmpc_last_kernel_ms(h, &kms);
     std::printf("{\"reset\": %.2f, \"set_options\": %.2f, \"set_model\": %.2f, \"set_target\": %.2f, \"solve_after_them\": %.2f, \"sequence\": %.2f, "
-                "\"solve_alone_cold\": %.2f, \"empty_sync\": %.2f, \"iters\": %u, \"launches\": %lld}\n",
-                p50(t_reset), p50(t_opt), p50(t_model), p50(t_target), p50(t_solve), p50(t_all), p50(t_solve_only), p50(t_sync), it,
+                "\"solve_alone_cold\": %.2f, \"empty_sync\": %.2f, \"iters\": %u, \"kernel_us\": %.1f, \"launches\": %lld}\n",
+                p50(t_reset), p50(t_opt), p50(t_model), p50(t_target), p50(t_solve), p50(t_all), p50(t_solve_only), p50(t_sync), it, kms * 1e3,
                 (long long)bmpc_launch_count(h));
     bmpc_destroy(h);
     return 0;

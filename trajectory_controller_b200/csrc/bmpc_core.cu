@@ -238,6 +238,7 @@ int bmpc_create(bmpc_t** out, int S, int I, int N, int64_t capacity, int precisi
     h->pair_direct_max = h->pair_threshold;
     if (const char* e = std::getenv("BMPC_PAIR_THRESHOLD")) h->pair_threshold = std::atoll(e);
     if (const char* e = std::getenv("BMPC_PAIR_DIRECT")) h->pair_direct_max = std::atoll(e);
+    if (const char* e = std::getenv("BMPC_SMALL")) h->small_cfg = std::atoi(e);
     if (h->pair_threshold < 0) h->pair_threshold = 0;
     if (ops->S == 4 && ops->I == 1 && h->pair_threshold > 0) {
         const size_t ct = (size_t)h->pair_threshold;

@@ -60,11 +60,12 @@ constexpr int kSmallVals = 64;
 struct SmallVals { double x[kSmallVals]; };
 struct PutPlan { int n; int off[8]; int len[8]; void* dst[8]; };
 cudaError_t put_vals(const SmallVals& v, const PutPlan& plan, long long first, long long count, long long stride, int elem_size,
-                     cudaStream_t st);
+                     cudaStream_t st, unsigned long long* zero8 = nullptr);
 constexpr int kSmallSolve = 16;    // solves of up to this many instances use the packed one-copy result path
 __host__ __device__ inline size_t small_results_err_offset(int count, int I) { return (((size_t)count * I * 8 + (size_t)count * 5) + 7) & ~(size_t)7; }
 cudaError_t pack_results(const void* u0, const uint32_t* iters, const uint8_t* status, const unsigned long long* queue, int count,
-                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st);
+                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st,
+                         unsigned long long* flag = nullptr, unsigned long long seq = 0);
 
 // bmpc_solve_resident_async on the instances [first, first + count) of the handle (cold solves with one target per
 // instance only: the fleet tick's chunks).
@@ -108,6 +109,10 @@ struct bmpc_handle {
     bmpc::DevBuf results;         // ONE allocation: u0 | iters | status (each 256-byte aligned) — u0 / iters / status below are views
     bmpc::DevBuf x0, u0, iters, status, controls, vstate, target_const, target_full, queue;
     bmpc::DevBuf pg_list, park, park_iter;   // split solve: hand-over ring and the by-slot state of parked instances (pg_kernel.cuh)
+    int small_cfg = 15;              // small-call shortcuts (developer knob BMPC_SMALL, bits: 1 counters zeroed by the x0 kernel,
+                                     // 2 no stage event, 4 results written to pinned host memory + polled, 8 one kernel where no pair kernel)
+    int small_now = 0;               // the bits in force for the solve being launched (small_solve sets and clears it)
+    unsigned long long small_seq = 0;
     bool ring_dirty = true;          // pg_list may hold entries of an earlier launch (bmpc_solve_resident_async)
     size_t pg_ring = 0;              // ring capacity (a power of two >= capacity + lanes in flight)
     bool sym_ok = false;             // the model meets the preconditions of stage B's symmetric-bound kernel (bmpc_set_model)

@@ -210,7 +210,9 @@ int bmpc::solve_range_async(bmpc_handle* h, long long first, long long count, un
     g.queue = (unsigned long long*)h->queue.p;
     // Two-stage solve (pg_kernel.cuh): needs the stage-B kernel for this shape, iterations beyond the 50 coordinate
     // steps, and eps > 0 (stage B tests "|df| >= eps" instead of carrying max_df; bmpc_set_options enforces eps > 0).
-    const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0;
+    // (a small call of a shape without a lane-pair kernel runs as ONE kernel: a launch and a hand-over less, same results)
+    const bool one_kernel_small = (h->small_now & 8) && !(h->solve_ops->has_pair && h->c_list.p != nullptr && h->pair && h->sym && h->sym_ok);
+    const bool split = h->split && h->solve_ops->has_pg && h->max_iter > 50 && h->eps > 0 && !one_kernel_small;
     g.split = split; g.pg_list = (uint32_t*)h->pg_list.p;
     g.sym = 0;
     if (split && h->sym_ok && h->sym) {   // the symmetric-bound stage-B kernel, where the shape has one (register-resident horizons)
@@ -248,7 +250,7 @@ int bmpc::solve_range_async(bmpc_handle* h, long long first, long long count, un
     // stage A's entries behind.  So the ring is wiped only when a recycling launch follows a non-recycling one.
     if (split && g.pg_reuse && h->ring_dirty) BMPC_CUDA(cudaMemsetAsync(h->pg_list.p, 0xff, h->pg_ring * 4, h->stream));
     if (split) h->ring_dirty = !g.pg_reuse;
-    BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));
+    if (!(h->small_now & 1)) BMPC_CUDA(cudaMemsetAsync(h->queue.p, 0, 64, h->stream));   // (small calls: zeroed by the x0 kernel)
     BMPC_CUDA(cudaEventRecord(h->ev0, h->stream));
     KernelInfo ki;
     BMPC_CUDA(h->solve_ops->info(h->precision, h->mode, h->per_instance, &ki));
@@ -264,9 +266,10 @@ int bmpc::solve_range_async(bmpc_handle* h, long long first, long long count, un
     g.warp_limit_a = limit_for(ki.warps);
     BMPC_CUDA(h->solve_ops->solve(h->precision, h->mode, h->per_instance, g, grid, h->stream));
     h->launches++;
-    h->timed_split = split;
+    const bool stage_event = split && !(h->small_now & 2);             // small calls: bmpc_last_stage_ms reports stage B as 0
+    h->timed_split = stage_event;
     if (split) {
-        BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
+        if (stage_event) BMPC_CUDA(cudaEventRecord(h->ev_mid, h->stream));
         if (!pair_direct) {
             KernelInfo kp;
             BMPC_CUDA(h->solve_ops->pg_info(h->precision, h->mode, h->per_instance, g.sym, &kp));
@@ -325,22 +328,45 @@ int bmpc_download(bmpc_t* h, int64_t count, double* u0, uint32_t* iters, uint8_t
 static int small_solve(bmpc_t* h, int count, const double* x0, double* u0, uint32_t* iters, uint8_t* status, unsigned flags)
 {
     BMPC_CUDA(cudaSetDevice(h->device));
+    const int opts = h->small_cfg;
     SmallVals v; PutPlan plan{};
     for (int b = 0; b < count; ++b) {        // one launch per instance keeps the argument block small; count is tiny
         plan.n = 1; plan.off[0] = 0; plan.len[0] = h->S; plan.dst[0] = h->x0.p;
         for (int e = 0; e < h->S; ++e) v.x[e] = x0[(size_t)b * h->S + e];
-        BMPC_CUDA(put_vals(v, plan, b, 1, h->cap, h->elem, h->stream));
+        // the first of them also zeroes the launch counters of the solve (instead of a memset of its own)
+        BMPC_CUDA(put_vals(v, plan, b, 1, h->cap, h->elem, h->stream, (b == 0 && (opts & 1)) ? (unsigned long long*)h->queue.p : nullptr));
         h->launches++;
     }
+    h->small_now = opts;
     int rc = bmpc_solve_resident_async(h, count, flags);
+    h->small_now = 0;
     if (rc) return rc;
     const size_t err_off = small_results_err_offset(count, h->I), bytes = err_off + 8;
-    BMPC_CUDA(pack_results(h->u0.p, (const uint32_t*)h->iters.p, (const uint8_t*)h->status.p, (const unsigned long long*)h->queue.p,
-                           count, h->I, h->cap, h->elem, (unsigned char*)h->small.p, h->stream));
-    h->launches++;
     unsigned char* pin = (unsigned char*)h->pinned;
-    BMPC_CUDA(cudaMemcpyAsync(pin, h->small.p, bytes, cudaMemcpyDeviceToHost, h->stream));
-    BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    if (opts & 4) {
+        // Results straight into the pinned host block (device-visible: unified addressing), then a sequence word the
+        // host polls: no copy operation and no stream synchronisation on the way back.
+        volatile unsigned long long* flag = (volatile unsigned long long*)(pin + bytes);
+        const unsigned long long seq = 0x5EED000000000000ull | (++h->small_seq & 0xffffffffffffull);   // never a plausible number another call leaves there
+        BMPC_CUDA(pack_results(h->u0.p, (const uint32_t*)h->iters.p, (const uint8_t*)h->status.p, (const unsigned long long*)h->queue.p,
+                               count, h->I, h->cap, h->elem, pin, h->stream, (unsigned long long*)flag, seq));
+        h->launches++;
+        for (unsigned spins = 1; *flag != seq; ++spins) {
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+            if ((spins & 0x3ffu) == 0) {     // a failed launch never writes the flag: ask the stream now and then
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q != cudaSuccess && q != cudaErrorNotReady) return bmpc::fail_cuda(q, "bmpc_solve (small call)");
+            }
+        }
+    } else {
+        BMPC_CUDA(pack_results(h->u0.p, (const uint32_t*)h->iters.p, (const uint8_t*)h->status.p, (const unsigned long long*)h->queue.p,
+                               count, h->I, h->cap, h->elem, (unsigned char*)h->small.p, h->stream));
+        h->launches++;
+        BMPC_CUDA(cudaMemcpyAsync(pin, h->small.p, bytes, cudaMemcpyDeviceToHost, h->stream));
+        BMPC_CUDA(cudaStreamSynchronize(h->stream));
+    }
     std::memcpy(u0, pin, (size_t)count * h->I * 8);
     if (iters) std::memcpy(iters, pin + (size_t)count * h->I * 8, (size_t)count * 4);
     if (status) std::memcpy(status, pin + (size_t)count * h->I * 8 + (size_t)count * 4, (size_t)count);
@@ -353,7 +379,7 @@ int bmpc_solve(bmpc_t* h, int64_t count, const double* x0, double* u0, uint32_t*
 {
     int rc;
     if (h && x0 && u0 && count >= 1 && count <= kSmallSolve && count <= h->cap && (long long)h->S <= kSmallVals &&
-        small_results_err_offset((int)count, h->I) + 8 <= h->pinned_bytes)
+        small_results_err_offset((int)count, h->I) + 16 <= h->pinned_bytes)
         return small_solve(h, (int)count, x0, u0, iters, status, flags);
     if ((rc = upload_x0_async(h, count, x0))) return rc;   // x0 stays valid: bmpc_download synchronises before returning
     if ((rc = bmpc_solve_resident_async(h, count, flags))) return rc;

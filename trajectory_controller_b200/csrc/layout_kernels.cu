@@ -208,8 +208,9 @@ __global__ void k_extract_horizon(long long count, int P, const int32_t* __restr
 // vals[off[a] .. off[a] + len[a]) -> dst[a][e * stride + b] for b in [first, first + count): `count` == capacity
 // broadcasts one vector to every instance (set_target(val)), count == 1 writes one instance (shared model, x0).
 template <typename T>
-__global__ void k_put_vals(SmallVals v, PutPlan plan, long long first, long long count, long long stride)
+__global__ void k_put_vals(SmallVals v, PutPlan plan, long long first, long long count, long long stride, unsigned long long* zero8)
 {
+    if (zero8 && blockIdx.x == 0 && threadIdx.x < 8) zero8[threadIdx.x] = 0ull;   // the launch counters of the solve that follows
     const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= count) return;
     for (int a = 0; a < plan.n; ++a) {
@@ -221,7 +222,8 @@ __global__ void k_put_vals(SmallVals v, PutPlan plan, long long first, long long
 // (padded to 8) | the launch's error word (queue[4]).
 template <typename T>
 __global__ void k_pack_results(const T* __restrict__ u0, const uint32_t* __restrict__ iters, const uint8_t* __restrict__ status,
-                               const unsigned long long* __restrict__ queue, int count, int I, long long stride, unsigned char* out)
+                               const unsigned long long* __restrict__ queue, int count, int I, long long stride, unsigned char* out,
+                               unsigned long long* flag, unsigned long long seq)
 {
     const int t = threadIdx.x;
     double* ou = reinterpret_cast<double*>(out);
@@ -231,6 +233,11 @@ __global__ void k_pack_results(const T* __restrict__ u0, const uint32_t* __restr
     for (int f = t; f < count * I; f += blockDim.x) ou[f] = (double)u0[(long long)(f % I) * stride + f / I];
     for (int b = t; b < count; b += blockDim.x) { oi[b] = iters[b]; os[b] = status[b]; }
     if (t == 0) *oe = queue[4];
+    if (flag) {   // `out` is pinned host memory the caller polls: everything above must be visible there before the flag
+        __threadfence_system();
+        __syncthreads();
+        if (t == 0) { *reinterpret_cast<volatile unsigned long long*>(flag) = seq; __threadfence_system(); }
+    }
 }
 
 inline unsigned blocks_for(long long count, int block) { return (unsigned)((count + block - 1) / block); }
@@ -292,19 +299,20 @@ cudaError_t launch_extract(long long count, int P, const int32_t* npoints, const
 }
 
 cudaError_t put_vals(const SmallVals& v, const PutPlan& plan, long long first, long long count, long long stride, int elem_size,
-                     cudaStream_t st)
+                     cudaStream_t st, unsigned long long* zero8)
 {
     if (count <= 0) return cudaSuccess;
     const int block = count < 128 ? 32 : 128;
-    if (elem_size == 8) k_put_vals<double><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride);
-    else k_put_vals<float><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride);
+    if (elem_size == 8) k_put_vals<double><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride, zero8);
+    else k_put_vals<float><<<blocks_for(count, block), block, 0, st>>>(v, plan, first, count, stride, zero8);
     return cudaGetLastError();
 }
 cudaError_t pack_results(const void* u0, const uint32_t* iters, const uint8_t* status, const unsigned long long* queue, int count,
-                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st)
+                         int I, long long stride, int elem_size, unsigned char* out, cudaStream_t st, unsigned long long* flag,
+                         unsigned long long seq)
 {
-    if (elem_size == 8) k_pack_results<double><<<1, 64, 0, st>>>((const double*)u0, iters, status, queue, count, I, stride, out);
-    else k_pack_results<float><<<1, 64, 0, st>>>((const float*)u0, iters, status, queue, count, I, stride, out);
+    if (elem_size == 8) k_pack_results<double><<<1, 64, 0, st>>>((const double*)u0, iters, status, queue, count, I, stride, out, flag, seq);
+    else k_pack_results<float><<<1, 64, 0, st>>>((const float*)u0, iters, status, queue, count, I, stride, out, flag, seq);
     return cudaGetLastError();
 }
 
